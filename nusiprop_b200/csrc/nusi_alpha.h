@@ -1,0 +1,330 @@
+// nusi_alpha.h -- the regeneration kernel  alpha(Em, Ep, Em', Ep')  : a neutrino of the source
+// bin [Em',Ep'] (variable s' = 2 m_k E'/mphi^2) scatters into the bin [Em,Ep] (t = -2 m_k E/mphi^2).
+// Restates calculate_flux::alpha (reference nuSIprop.hpp:1237-1520).  This is the O(NT^2) part
+// of the table build and 65-85 % of the reference's evolve() time.
+//
+// B200-first structure.  All bins are cells of one log-uniform edge grid, so every
+// transcendental of the closed forms depends on at most ONE row edge t and ONE column edge s:
+//   RowEdge(t)    ln(1-t), ln|1+t|, ln(1+(2+t)^2/ga^2), arg(-1/(1+t))           O(NT) per mass
+//   ColEdge(s)    ln s, ln(1+(s-1)^2/ga^2), arg(s-1+i ga), ln((2+s)/s), ...     O(NT) per mass
+//   Vertex(s,t)   ln(1+s+t), three real Li2, one complex Li2, one arg           O(NT^2) per mass
+// and a cell only combines its 2 row edges, 2 column edges and 4 vertices with + - * / (plus
+// four ratio-logarithms of the t channel).  Neighbouring cells share edges and vertices, which
+// is what the tiled kernel exploits; the per-cell arithmetic below keeps the reference's term
+// order so that the same inputs round the same way.
+#ifndef NUSI_ALPHA_H
+#define NUSI_ALPHA_H
+#include "nusi_aux.h"
+#include "nusi_interp.h"
+
+namespace nusi {
+
+struct RowEdge {
+  double t;      // t/mphi^2 at the edge, already moved off the pole t = -1 (nuSIprop.hpp:1257-1262)
+  double l1m;    // log1p(-t)
+  double labs;   // ln|1+t| as nuSIprop.hpp:1386-1387 computes it
+  double lfabs;  // log(fabs(1+t)) as the s-t interference writes it (nuSIprop.hpp:1456)
+  double lam2;   // log1p((2+t)^2/ga_red^2)
+  double argn;   // carg(-(1/(1+t))): pi if 1+t > 0 else 0
+};
+struct ColEdge {
+  double s;      // s'/mphi^2 at the edge
+  double ls;     // log(s)
+  double lam;    // log1p((s-1)^2/ga_red^2)
+  double args;   // carg(-1 + i ga_red + s)
+  double l2s;    // log((2+s)/s)
+  double ls2;    // log(s/(2+s))
+};
+struct Vertex {
+  double l1;     // log1p(s+t)
+  double lf;     // log(1+s+t)
+  double dF;     // t < -1 ? Li2((1+s+t)/s) : Li2(s/(1+s+t))
+  double lq;     // log((1+s+t)/s)          (used only when t >= -1)
+  double d2;     // Li2((1+s+t)/(2+s))
+  double zr_re, zr_im;  // gsl-style complex Li2 of the REAL number (1+s+t)/(1+t)
+  double zc_re, zc_im;  // complex Li2 of (1+s+t)/(2 - i ga_red + t)
+  double ca;     // carg(-((-1 + i ga_red + s)/(2 - i ga_red + t)))
+};
+
+NUSI_HD double t_of(double mn, double E, double mphi) {
+  double t = -2 * mn * E / sqr(mphi);
+  if (fabs(t + 1) < 1e-7) t += t * 1e-6;
+  return t;
+}
+NUSI_HD double s_of(double mn, double E, double mphi) { return 2 * mn * E / sqr(mphi); }
+
+NUSI_HD void make_row_edge(double t, double gr, bool full, RowEdge &R) {
+  R.t = t;
+  R.l1m = log1p(-t);
+  if (full) {
+    R.labs = (t > -1) ? log1p(t) : log(-1 - t);
+    R.lfabs = log(fabs(1 + t));
+    R.lam2 = log1p(sqr(2 + t) / sqr(gr));
+    R.argn = (-(1 / (1 + t)) < 0) ? kPi : 0.0;
+  }
+}
+NUSI_HD void make_col_edge(double s, double gr, bool full, ColEdge &C) {
+  C.s = s;
+  C.ls = log(s);
+  C.lam = log1p(sqr(-1 + s) / sqr(gr));
+  C.args = atan2(gr, -1 + s);
+  if (full) {
+    C.l2s = log((2 + s) / s);
+    C.ls2 = log(s / (2 + s));
+  }
+}
+// everything of the Majorana closed forms that depends on one (s, t) pair
+NUSI_HD void make_vertex(double s, double t, double gr, Vertex &V) {
+  const double one_st = 1 + s + t;
+  V.l1 = log1p(s + t);
+  V.lf = log(one_st);
+  if (t < -1) {
+    V.dF = li2_real(one_st / s);
+    V.lq = 0.0;
+  } else {
+    V.dF = li2_real(s / one_st);
+    V.lq = log(one_st / s);
+  }
+  V.d2 = li2_real(one_st / (2 + s));
+  const double zr = one_st / (1 + t);
+  V.zr_re = li2_real(zr);
+  V.zr_im = (zr >= 1.0) ? -kPi * log(zr) : 0.0;
+  const cplx den = mk(2 + t, -gr);
+  const cplx zc = one_st / den;
+  const cplx dc = cli2(zc.re, zc.im);
+  V.zc_re = dc.re;
+  V.zc_im = dc.im;
+  V.ca = carg_(-(mk(-1 + s, gr) / den));
+}
+
+// 3x3 Gauss-Legendre fallback on  y in [t+, t-], x in [s-, s+]  (nuSIprop.hpp:1288-1303 etc.)
+// KIND 0: t and u propagators (Majorana t), 1: single propagator (Dirac t, u), 2: t-u interference
+template <int KIND>
+NUSI_HD double alpha_gl2d(double tplus, double tminus, double sminus, double splus) {
+  const double a_y = tplus, b_y = tminus, a_x = sminus, b_x = splus;
+  double acc = 0;
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      const double y = (b_y - a_y) / 2. * gl_x(i) + (b_y + a_y) / 2.;
+      const double x = (b_x - a_x) / 2. * gl_x(j) + (b_x + a_x) / 2.;
+      double F;
+      if (KIND == 0)
+        F = sqr(y / x) / sqr(y - 1) + sqr((-x - y) / x) / sqr((-x - y) - 1);
+      else if (KIND == 1)
+        F = sqr(y / x) / sqr(y - 1);
+      else
+        F = 2 * y * (-y - x) / sqr(x) / ((y - 1) * (-y - x - 1));
+      acc += gl_w(i) * gl_w(j) * F;
+    }
+  acc *= 1. / 4. * (b_y - a_y) * (b_x - a_x);
+  return acc;
+}
+
+// s-channel factor of a source bin: everything of alpha_s except (t- - t+)   (nuSIprop.hpp:1265-1269)
+NUSI_HD double alpha_s_colfactor(const PointParams &P, double sminus, double splus) {
+  const double mphi = P.mphi, Ga = P.Ga;
+  if (splus < 1e-5) {
+    const double gr = Ga / mphi;
+    return (gr * (1 + sqr(gr) + 2 * sminus)) / sqr(1 + sqr(gr)) * (splus - sminus) +
+           (gr) / sqr(1 + sqr(gr)) * sqr(splus - sminus);
+  }
+  return atandiff(mphi * (splus - 1) / Ga, mphi * (sminus - 1) / Ga);
+}
+
+// double-scalar production, asymptotic forms above the tabulated range (nuSIprop.hpp:1487-1492)
+NUSI_HD double alpha_pp_asymptotic(double sm, double sp, double tm, double tp) {
+  const double lsm = log(sm), lsp = log(sp);
+  const double tail = (-6 * sm + 6 * sp - 2 * (-2 + sm) * sp * lsm + sm * sp * sqr(lsm) + 2 * sm * (-2 + sp) * lsp -
+                       sm * sp * sqr(lsp));
+  if (tm < -1) {
+    const double a = log(-1 - tm), b = log(-tm), c = log(-1 - tp), d = log(-tp);
+    return ((-sm + sp) * ((tm - tp) * (sp * (-2 + tm + tp) + sm * (-2 - 24 * sp + tm + tp)) +
+                          4 * (-(sp * (1 + tm)) + sm * (-1 + 2 * sp + (-1 + sp) * tm)) * a +
+                          2 * (3 * sp + sm * (3 + 4 * sp)) * tm * b +
+                          4 * (sp + sp * tp + sm * (1 + tp - sp * (2 + tp))) * c -
+                          2 * (3 * sp + sm * (3 + 4 * sp)) * tp * d) +
+            2 * sqr(sm) * lsp *
+                ((3 + 2 * sp) * (tm - tp) + 2 * sqr(sp) * ((-1 - tm) * a + tm * b + (1 + tp) * c - tp * d)) +
+            2 * sqr(sp) * lsm *
+                ((-3 - 2 * sm) * (tm - tp) + 2 * sqr(sm) * ((1 + tm) * a - tm * b - (1 + tp) * c + tp * d))) /
+           (256. * kPi * sqr(sm) * sqr(sp));
+  } else if (tp < -1) {
+    const double c = log(-1 - tp), d = log(-tp);
+    return ((2 * sqr(sm) * lsp * ((1 + tp) * (-3 - 2 * sp + 2 * sqr(sp) * c) - 2 * sqr(sp) * tp * d) +
+             (sm - sp) * ((1 + tp) * (-3 * (sm + sp + 8 * sm * sp) + (sm + sp) * tp) +
+                          4 * (-(sp * (1 + tp)) + sm * (-1 + 2 * sp + (-1 + sp) * tp)) * c +
+                          2 * (3 * sp + sm * (3 + 4 * sp)) * tp * d) +
+             2 * sqr(sp) * lsm * ((3 + 2 * sm) * (1 + tp) + 2 * sqr(sm) * (-((1 + tp) * c) + tp * d))) /
+                (256. * kPi * sqr(sm) * sqr(sp)) +
+            (-1 - tm) * tail / (128. * kPi * sm * sp));
+  }
+  return (tp - tm) * tail / (128. * kPi * sm * sp);
+}
+
+// Contribution of target mass k to one table entry, added channel by channel to `tot`.
+//   Rm,Rp  row edges t-, t+      Cm,Cp  column edges s'-, s'+
+//   Vmm = (s-,t-)  Vpm = (s+,t-)  Vmp = (s-,t+)  Vpp = (s+,t+)   (vertices: only Majorana non-resonant)
+//   fs = alpha_s_colfactor of the source bin
+NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k, double fs, const RowEdge &Rm,
+                             const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, const Vertex &Vmm,
+                             const Vertex &Vpm, const Vertex &Vmp, const Vertex &Vpp, double &tot, int *warn) {
+  const double mphi = P.mphi, g = P.g, Ga = P.Ga;
+  const double g4 = sqr(sqr(g)), m4 = sqr(sqr(mphi));
+  const double U2 = P.U2f[k];
+  const double wgt = m4 / (2 * P.mn[k]);
+  const double tm = Rm.t, tp = Rp.t, sm = Cm.s, sp = Cp.s;
+
+  /* s channel */
+  double a_s = g4 / (8 * kPi * Ga * cub(mphi)) * (tm - tp) * fs;
+  a_s *= U2;
+  if (!P.majorana) a_s /= 2.;
+  tot += wgt * a_s;
+  if (!P.non_resonant) return;
+
+  double a_t, a_u, a_tu, a_st;
+  const double gr = Ga / mphi;
+  if (P.majorana) {
+    /* t channel (u is identical for Majorana) */
+    const double LR1 = log(((1 + sm + tm) * (-1 + tp)) / ((-1 + tm) * (1 + sm + tp)));
+    const double LR2 = log(((1 + sp + tm) * (-1 + tp)) / ((-1 + tm) * (1 + sp + tp)));
+    const double LYm = log((sm * (1 + sp + tm)) / (sp * (1 + sm + tm)));
+    const double LYp = log((sm * (1 + sp + tp)) / (sp * (1 + sm + tp)));
+    const double N1 = sm * sp * (-tm + tp) * Cm.ls + sm * sp * (tm - tp) * Cp.ls - sm * sp * Vmm.l1 -
+                      sm * sp * tp * Vmm.l1 + sm * sp * Vpm.l1 + sm * sp * tp * Vpm.l1 - sp * LR1 - sp * tm * LR1 -
+                      sp * tp * LR1 - sp * tm * tp * LR1 + sm * sp * Vmp.lf + sm * sp * tm * Vmp.l1 + sm * LR2 +
+                      sm * tm * LR2 + sm * tp * LR2 + sm * tm * tp * LR2 - sm * sp * Vpp.lf - sm * sp * tm * Vpp.l1;
+    a_t = g4 / (sm * sp * 16 * kPi * m4) *
+          (-((sm - sp) * (3 + 2 * tm * (-1 + tp) - 2 * tp) * (tm - tp)) / ((-1 + tm) * (-1 + tp)) +
+           2 * (N1) / ((1 + tm) * (1 + tp)) -
+           ((sm * sp * LYm) / sqr(1 + tm) +
+            (((sm - sp) * (tm - tp) * (1 + tp)) / (1 + tm) - sm * sp * LYp) / sqr(1 + tp)));
+    if (a_t < 0) a_t = alpha_gl2d<0>(tp, tm, sm, sp) * (g4 / (16 * kPi * m4));
+    a_t *= U2;
+    a_u = a_t;
+  } else {
+    const double core = (-((tm - tp) * (2 + tm * (-1 + tp) - tp)) - 2 * (-1 + tm) * (-1 + tp) * (Rm.l1m - Rp.l1m));
+    a_t = 3. / 2. * g4 / (32 * kPi * m4 * sm * sp * (-1 + tm) * (-1 + tp)) * (sm - sp) * core;
+    if (a_t < 0) a_t = alpha_gl2d<1>(tp, tm, sm, sp) * (3. / 2. * g4 / (32 * kPi * m4));
+    a_t *= U2;
+    a_u = 1. / 2. * g4 / (32 * kPi * m4 * sm * sp * (-1 + tm) * (-1 + tp)) * (sm - sp) * core;
+    if (a_u < 0) a_u = alpha_gl2d<1>(tp, tm, sm, sp) * (1. / 2. * g4 / (32 * kPi * m4));
+    a_u *= U2;
+  }
+  tot += wgt * a_t;
+  tot += wgt * a_u;
+
+  /* t-u interference (Majorana only) */
+  if (P.majorana) {
+    double F_tp, F_tm;
+    if (tp < -1)
+      F_tp = Vmp.dF - Vpp.dF;
+    else
+      F_tp = -Vmp.dF + Vpp.dF - 0.5 * (sqr(Vmp.lq) - sqr(Vpp.lq));
+    if (tm < -1)
+      F_tm = -Vmm.dF + Vpm.dF;
+    else
+      F_tm = Vmm.dF - Vpm.dF + 0.5 * (sqr(Vmm.lq) - sqr(Vpm.lq));
+    const double lmp = log(sm / sp);
+    a_tu = g4 / (32 * kPi * m4 * sm * sp * (1 + tm) * (1 + tp)) *
+           (-4 * (sm - sp) * (1 + tm) * (tm - tp) * (1 + tp) + 2 * sm * sp * tp * (lmp - Vmm.l1 + Vpm.l1) +
+            2 * sp * (1 + tm) * (1 + tp) * (Rm.l1m - Vmm.l1 - Rp.l1m + Vmp.l1) -
+            2 * sm * (1 + tm) * (1 + tp) * (Rm.l1m - Vpm.l1 - Rp.l1m + Vpp.l1) +
+            2 * sm * sp * (-Vmm.l1 + Vpm.l1 + Vmp.l1 - Vpp.l1) +
+            sm * sp * (1 + tm) * (1 + tp) *
+                (Cm.l2s * (Cp.ls + Vmp.l1) - Cp.l2s * (Cm.ls + Vpp.l1) + Rp.l1m * (lmp - Vmp.l1 + Vpp.l1)) +
+            sm * sp * (1 + tm) * (1 + tp) *
+                ((Cp.ls + Vmm.l1) * (Cm.ls2 + Rm.l1m - Rm.labs) + (Cm.ls + Vpm.l1) * (Cp.l2s - Rm.l1m + Rm.labs)) +
+            sm * sp * (log(sp / sm) + Vmp.l1 - Vpp.l1) * (2 * tm + (1 + tm) * (1 + tp) * Rp.labs) +
+            sm * sp * (1 + tm) * (1 + tp) * (Vmm.d2 - Vpm.d2 - Vmp.d2 + Vpp.d2) +
+            sm * sp * (1 + tm) * (1 + tp) * (F_tp + F_tm));
+    // NB: the reference's quadrature fallback for a negative alpha_tu assigns to a shadowing local
+    // (nuSIprop.hpp:1406) and therefore has no effect; a negative value is kept.
+  } else {
+    a_tu = 0.;
+  }
+  a_tu *= U2;
+  tot += wgt * a_tu;
+
+  /* s-t interference */
+  if (P.majorana) {
+    const double dS = 2 * (tm - tp) + (Rm.l1m - Rp.l1m);
+    a_st = g4 / (32 * kPi * (1 + sqr(gr)) * m4) *
+           (2 * gr * (Vmm.zr_im - Vmm.zc_im - Vpm.zr_im + Vpm.zc_im - Vmp.zr_im + Vmp.zc_im + Vpp.zr_im - Vpp.zc_im) -
+            2 * (Vmm.zr_re - Vmm.zc_re - Vpm.zr_re + Vpm.zc_re - Vmp.zr_re + Vmp.zc_re + Vpp.zr_re - Vpp.zc_re) +
+            2 * gr * (Rm.argn - Vmm.ca) * Vmm.l1 - 2 * gr * (Rm.argn - Vpm.ca) * Vpm.l1 +
+            2 * gr * (Rp.argn - Vpp.ca) * Vpp.l1 - 2 * gr * (Rp.argn - Vmp.ca) * Vmp.l1 +
+            2 * (gr * Cm.args - gr * Cp.args + Cp.lam / 2. - Cm.lam / 2. + Cm.ls - Cp.ls) * dS +
+            Vmm.l1 * (Cm.lam - Rm.lam2 - 2 * (Cm.ls - Rm.lfabs)) - Vpm.l1 * (Cp.lam - Rm.lam2 - 2 * (Cp.ls - Rm.lfabs)) -
+            Vmp.l1 * (Cm.lam - Rp.lam2 - 2 * (Cm.ls - Rp.lfabs)) + Vpp.l1 * (Cp.lam - Rp.lam2 - 2 * (Cp.ls - Rp.lfabs)));
+  } else {
+    a_st = g4 / (32 * kPi * (1 + sqr(gr)) * m4) *
+           ((2 * gr * Cm.args - 2 * gr * Cp.args + 2 * Cm.ls - 2 * Cp.ls + Cp.lam - Cm.lam) *
+            (tm - tp + Rm.l1m - Rp.l1m));
+  }
+  a_st *= U2;
+  tot += wgt * a_st;
+
+  /* s-u interference: Majorana only */
+  const double a_su = P.majorana ? a_st : 0.;
+  tot += wgt * a_su;
+
+  /* double-scalar production */
+  double a_pp = 0;
+  if ((sm > 4) && P.phiphi) {
+    if (sm < 1e4) {
+      const double delta = sp / sm;
+      a_pp = g4 / m4 * fabs(phiphi_alpha_eval(pp, sm, log(-sm / tm) / log(delta) * 1.0001, log10(delta), warn));
+    } else {
+      a_pp = g4 / m4 * alpha_pp_asymptotic(sm, sp, tm, tp);
+    }
+    a_pp *= U2;
+    if (P.majorana) a_pp *= 2;
+    a_pp *= 2;
+    if (P.majorana) a_pp *= 2;
+  }
+  tot += wgt * a_pp;
+
+  const double nrm = sqr(sqr(g / mphi));
+  if (warn && (a_s < 0 || a_t / nrm < -1e-11 || a_u / nrm < -1e-11 || a_tu / nrm < -1e-11 ||
+               (a_st + a_s + a_t) / nrm < -1e-11))
+    *warn |= NUSI_WARN_ALPHA;
+}
+
+// One table entry computed from scratch (no sharing): used by the straightforward kernel and
+// by the host-side checks.  Em..Ep is the target bin (row), Emp..Epp the source bin (column).
+NUSI_HD double alpha_entry(const PointParams &P, const PhiPhiTables *pp, double Em, double Ep, double Emp, double Epp,
+                           int *warn) {
+  double tot = 0;
+  const double gr = P.Ga / P.mphi;
+  const bool full = P.non_resonant && P.majorana;
+  for (int k = 0; k < 3; ++k) {
+    RowEdge Rm, Rp;
+    ColEdge Cm, Cp;
+    Vertex Vmm, Vpm, Vmp, Vpp;
+    const double tm = t_of(P.mn[k], Em, P.mphi), tp = t_of(P.mn[k], Ep, P.mphi);
+    const double sm = s_of(P.mn[k], Emp, P.mphi), sp = s_of(P.mn[k], Epp, P.mphi);
+    const double fs = alpha_s_colfactor(P, sm, sp);
+    if (P.non_resonant) {
+      make_row_edge(tm, gr, full, Rm);
+      make_row_edge(tp, gr, full, Rp);
+      make_col_edge(sm, gr, full, Cm);
+      make_col_edge(sp, gr, full, Cp);
+      if (full) {
+        make_vertex(sm, tm, gr, Vmm);
+        make_vertex(sp, tm, gr, Vpm);
+        make_vertex(sm, tp, gr, Vmp);
+        make_vertex(sp, tp, gr, Vpp);
+      }
+    } else {
+      Rm.t = tm;
+      Rp.t = tp;
+      Cm.s = sm;
+      Cp.s = sp;
+    }
+    alpha_cell_mass(P, pp, k, fs, Rm, Rp, Cm, Cp, Vmm, Vpm, Vmp, Vpp, tot, warn);
+  }
+  return tot;
+}
+
+}  // namespace nusi
+#endif

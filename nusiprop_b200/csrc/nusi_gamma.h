@@ -1,0 +1,144 @@
+// nusi_gamma.h -- bin-integrated absorption rate  Gamma(Em, Ep)  of one table row.
+// Restates calculate_flux::Gamma (reference nuSIprop.hpp:759-922): per target mass j the
+// s channel, t+u, the t-u, s-t and s-u interferences and double-scalar production, with the
+// reference's Taylor switches (splus < 1e-5) and its Gauss-Legendre fallbacks when a closed
+// form comes out negative.
+#ifndef NUSI_GAMMA_H
+#define NUSI_GAMMA_H
+#include "nusi_aux.h"
+
+namespace nusi {
+
+// integrands of the three fallbacks (nuSIprop.hpp:809, 833, 900)
+NUSI_HD double gamma_tu_sum_integrand(double z) { return (z + 2) / (z * (z + 1)) - 2 / sqr(z) * log1p(z); }
+NUSI_HD double gamma_tu_intf_integrand(double z) {
+  return 1 / z - 2 * (1 + z) / (sqr(z) * (2 + z)) * log1p(z);
+}
+NUSI_HD double gamma_pp_integrand(double z) {
+  const double q = sqrt(z * (z - 4));
+  return (sqr(z) - 4 * z + 6) / (sqr(z) * (z - 2)) * log(sqr((q + z - 2) / (q - z + 2))) - 6 * q / sqr(z);
+}
+template <double (*F)(double)>
+NUSI_HD double gl3(double a, double b) {
+  const double h = (b - a) / 2., c = (b + a) / 2.;
+  const double z1 = h * gl_x(0) + c, z2 = h * gl_x(1) + c, z3 = h * gl_x(2) + c;
+  return h * (gl_w(0) * F(z1) + gl_w(1) * F(z2) + gl_w(2) * F(z3));
+}
+
+// closed form of the double-scalar absorption between a (>= 4) and b  (nuSIprop.hpp:885-887;
+// the reference's second copy is the same expression with the literal 4 in place of sminus)
+NUSI_HD double gamma_pp_closed(double a, double b) {
+  const double qa = sqrt((-4 + a) * a), qb = sqrt((-4 + b) * b);
+  const double ra = sqrt((-4 + a) / a), rb = sqrt((-4 + b) / b);
+  const double sa = sqrt(-4 + a), sb = sqrt(-4 + b), wa = sqrt(a), wb = sqrt(b);
+  return 12 * ra - 12 * rb - 2 * log(sqr(sa - wa) / 4.) * log(sqr(-2 + a + qa) / 4.) -
+         ((6 + a * log((-2 + a) * a)) * log(sqr(-2 + a + qa) / sqr(2 - a + qa))) / a -
+         24 * (ra - rb - log(sa + wa) + log(sb + wb)) +
+         2 * log(sqr(sb - wb) / 4.) * log(sqr(-2 + b + qb) / 4.) +
+         ((6 + b * log((-2 + b) * b)) * log(sqr(-2 + b + qb) / sqr(2 - b + qb))) / b +
+         8 * dilogdiff(4 / sqr(sa + wa), 4 / sqr(sb + wb)) +
+         2 * dilogdiff(4 / sqr(-2 + a + qa), 4 / sqr(-2 + b + qb));
+}
+
+// adds the contribution of target mass j to the running total `tot` of Gamma(Em, Ep), channel by
+// channel in the reference's order; *warn is set when the reference would print its
+// "Negative cross section when computing Gamma" message.
+NUSI_HD void gamma_mass(const PointParams &P, int j, double Em, double Ep, double &tot, int *warn) {
+  const double mphi = P.mphi, g = P.g, Ga = P.Ga;
+  const double g4 = sqr(sqr(g));
+  const double U2 = P.U2f[j];
+  const double wgt = sqr(mphi) / (2 * P.mn[j]);
+  const double splus = 2 * P.mn[j] * Ep / sqr(mphi);
+  const double sminus = 2 * P.mn[j] * Em / sqr(mphi);
+
+  /* s channel: Breit-Wigner integrated over the bin */
+  const double bw = sqr(mphi) / (sqr(mphi) + sqr(Ga));
+  const double dlog = log1p(bw * splus * (splus - 2)) - log1p(bw * sminus * (sminus - 2));
+  double Gs;
+  if (splus < 1e-5) {
+    const double gr = Ga / mphi;
+    Gs = g4 / (32 * kPi * sqr(mphi) * Ga) *
+         (2 * mphi *
+              ((gr * (1 + sqr(gr) + 2 * sminus)) / sqr(1 + sqr(gr)) * (splus - sminus) +
+               (gr) / sqr(1 + sqr(gr)) * sqr(splus - sminus)) +
+          Ga * dlog);
+  } else {
+    Gs = g4 / (32 * kPi * sqr(mphi) * Ga) *
+         (2 * mphi * atandiff(mphi * (splus - 1) / Ga, mphi * (sminus - 1) / Ga) + Ga * dlog);
+  }
+  Gs *= U2;
+  tot += wgt * Gs;
+  if (!P.non_resonant) return;
+
+  const double l1p = log1p(splus), l1m = log1p(sminus);
+
+  /* t + u without interference */
+  double Gtu_sum = g4 / (16 * kPi * sqr(mphi)) * (2 * l1p / splus - 2 * l1m / sminus + l1p - l1m);
+  if (Gtu_sum < 0) Gtu_sum = g4 / (16 * kPi * sqr(mphi)) * gl3<gamma_tu_sum_integrand>(sminus, splus);
+  Gtu_sum *= 2 * U2;  // same factor for Majorana and Dirac (nuSIprop.hpp:812-815)
+  tot += wgt * Gtu_sum;
+
+  /* t-u interference */
+  double Gtu = g4 / (32 * kPi * sqr(mphi) * sminus * splus) *
+               (sminus * l1p * (2 + 2 * splus + splus * log(2 + splus)) -
+                splus * l1m * (2 + 2 * sminus + sminus * log(2 + sminus)) +
+                sminus * splus * (dilog1mdiff(splus, sminus) + dilogdiff(splus, sminus)));
+  if (Gtu < 0) Gtu = g4 / (16 * kPi * sqr(mphi)) * gl3<gamma_tu_intf_integrand>(sminus, splus);
+  Gtu *= P.majorana ? U2 : 0.5 * U2;
+  tot += wgt * Gtu;
+
+  /* s-t interference */
+  const double gr = Ga / mphi;
+  const cplx den = mk(gr, 2.0);                       // 2i + ga_red
+  const cplx z1p = mk(0.0, 1 + splus) / den;          // i(1+s+)/(2i+ga_red)
+  const cplx z1m = mk(0.0, 1 + sminus) / den;
+  const cplx z2p = conj(z1p), z2m = conj(z1m);
+  cplx dd1, dd2;
+  if (splus < 1e-5) {
+    const cplx ip = mk(gr, 1.0), im = mk(gr, -1.0);   // i+ga_red, -i+ga_red
+    const cplx c1 = clog_(ip / den);
+    const cplx c2 = clog_(im / mk(gr, -2.0));
+    const cplx I = mk(0.0, 1.0);
+    dd1 = sqr(sminus) * ((-(I / 2.0)) / ip - c1 / 2.) + sminus * c1 - splus * c1 +
+          (sqr(splus) * (I / ip + c1)) / 2.;
+    dd2 = sqr(sminus) * ((I / 2.0) / im - c2 / 2.) + sminus * c2 - splus * c2 +
+          (sqr(splus) * ((-I) / im + c2)) / 2.;
+  } else {
+    dd1 = dilogdiff_complex(z1p, z1m);
+    dd2 = dilogdiff_complex(z2p, z2m);
+  }
+  const double lam_p = log1p(sqr(-1 + splus) / sqr(gr)), lam_m = log1p(sqr(-1 + sminus) / sqr(gr));
+  double Gst = -g4 / (32 * kPi * sqr(mphi) * (1 + sqr(gr))) *
+               (dd1.re + dd2.re + gr * (dd2.im - dd1.im) + 2 * gr * carg_(1.0 - z2p) * l1p -
+                2 * gr * carg_(1.0 - z2m) * l1m + log1p(4 / sqr(gr)) * (l1m - l1p) + lam_p * l1p -
+                lam_m * l1m + (1 + sqr(gr)) * (lam_m - lam_p) + 2 * dilogdiff(splus, sminus));
+  Gst *= U2;
+  tot += wgt * Gst;
+
+  /* s-u interference: Majorana only */
+  const double Gsu = P.majorana ? Gst : 0.0;
+  tot += wgt * Gsu;
+
+  /* double-scalar production above threshold s = 4 mphi^2 */
+  double Gpp = 0;
+  if ((splus > 4) && P.phiphi) {
+    const double a = (sminus > 4) ? sminus : 4.0;
+    Gpp = g4 / (128. * kPi * sqr(mphi)) * gamma_pp_closed(a, splus);
+    if (Gpp < 0) Gpp = g4 / (64 * kPi * sqr(mphi)) * gl3<gamma_pp_integrand>((sminus < 4) ? 4 : sminus, splus);
+    Gpp *= U2;
+    if (P.majorana) Gpp *= 2;
+  }
+  tot += wgt * Gpp;
+
+  if (warn && (Gs < 0 || Gtu_sum < 0 || Gtu < 0 || (Gs + Gtu_sum + Gst + Gsu) < 0)) *warn |= 1;
+}
+
+// Gamma(Em, Ep) = sum over the three target masses, accumulated in mass order like the reference
+NUSI_HD double gamma_row(const PointParams &P, double Em, double Ep, int *warn) {
+  double tot = 0;
+  for (int j = 0; j < 3; ++j) gamma_mass(P, j, Em, Ep, tot, warn);
+  return tot;
+}
+
+}  // namespace nusi
+#endif
