@@ -1,0 +1,136 @@
+/* nusiprop_b200.h -- C ABI of the B200-native nuSIprop redshift-evolution path.
+ *
+ * This is the drop-in boundary: plain C types, caller-owned buffers, no exceptions, no torch
+ * types.  The reference has no FFI of its own -- its public surface for this path is the
+ * header-only C++ class nuSIprop::calculate_flux (reference nuSIprop.hpp:22-540) and the Cython
+ * wrapper pyprop (reference nuSIprop.pyx:12-144).  Each entry point below names the reference
+ * interface it replaces; the drop-in class in nusiprop_b200/cxx/nuSIprop.hpp and the Python
+ * mirror in nusiprop_b200/pyprop.py are thin callers of this ABI.
+ *
+ * Threading: calls on ONE context must be serialised by the caller; distinct contexts are
+ * independent.  All functions return NUSI_OK (0) or a negative NUSI_E_* code;
+ * nusi_strerror() maps codes to text.  There is no CPU compute path: without a CUDA device
+ * nusi_ctx_create fails with NUSI_E_NO_DEVICE.
+ */
+#ifndef NUSIPROP_B200_H
+#define NUSIPROP_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NUSI_ABI_VERSION 1
+
+/* error codes (function return values) */
+#define NUSI_OK 0
+#define NUSI_E_INVALID (-1)   /* bad argument */
+#define NUSI_E_NO_DEVICE (-2) /* no usable CUDA device / wrong architecture */
+#define NUSI_E_CUDA (-3)      /* CUDA runtime error; see nusi_last_error() */
+#define NUSI_E_TABLE (-4)     /* phi-phi table file missing or malformed (reference: interp.hpp:251-254 exit(1)) */
+#define NUSI_E_NOMEM (-5)
+
+/* per-point status bits written by the evolve calls (0 = clean) */
+#define NUSI_ST_WARN_GAMMA 1      /* reference prints "Negative cross section when computing Gamma"      nuSIprop.hpp:909 */
+#define NUSI_ST_WARN_ALPHATILDE 2 /* ... alphaTilde                                                     nuSIprop.hpp:1215 */
+#define NUSI_ST_WARN_ALPHA 4      /* ... alpha                                                          nuSIprop.hpp:1505 */
+#define NUSI_ST_PP_RANGE 8        /* phi-phi lookup outside the table (reference: exit(1))              interp.hpp:355-361 */
+#define NUSI_ST_NO_MASS 256       /* no neutrino mass spectrum for this mntot (reference: exit(1))      aux.hpp:48-49 */
+
+typedef struct nusi_ctx nusi_ctx;       /* one (device, option set): grids, source term, tables */
+typedef struct nusi_points nusi_points; /* a batch of prepared parameter points resident in HBM */
+
+/* Fixed options of a context = the constructor arguments of calculate_flux that are NOT the
+ * mutable public members (reference nuSIprop.hpp:61-65): majorana, non_resonant,
+ * normal_ordering, N_bins_E, lEmin, lEmax, zmax, flav, phiphi. */
+typedef struct nusi_opts {
+  int majorana;          /* default 1 */
+  int non_resonant;      /* default 1 */
+  int normal_ordering;   /* default 1 */
+  int N_bins_E;          /* default 300 */
+  double lEmin;          /* default 12.0 */
+  double lEmax;          /* default 17.0 */
+  double zmax;           /* default 5.0 */
+  int flav;              /* default 2 */
+  int phiphi;            /* default 0 (C++ default; the Python wrapper defaults to 1, nuSIprop.pyx:52) */
+  const char *alphatilde_phiphi_path; /* NULL -> "xsec/alphatilde_phiphi.bin" relative to CWD (nuSIprop.hpp:168) */
+  const char *alpha_phiphi_path;      /* NULL -> "xsec/alpha_phiphi.bin"      (nuSIprop.hpp:169) */
+  int device;            /* CUDA device ordinal, default 0 */
+  int max_points_per_launch; /* 0 = choose from free HBM */
+} nusi_opts;
+
+/* Fills *o with the reference's C++ constructor defaults (nuSIprop.hpp:61-65). */
+int nusi_opts_default(nusi_opts *o);
+
+/* Replaces calculate_flux::calculate_flux(...) for everything that does not depend on
+ * (mphi, g, mntot): energy and redshift grids (nuSIprop.hpp:113-128), PMNS matrix (:130-163),
+ * phi-phi table load (:166-170), and the source term Lum(z_i, bin j) (:638-662), which is
+ * evaluated once by a CUDA kernel and kept in HBM. */
+int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o);
+void nusi_ctx_destroy(nusi_ctx *c);
+
+/* get_N_bins_E() (nuSIprop.hpp:407); N_steps_z and the effective zmax = z[N_steps_z-1]
+ * (nuSIprop.hpp:124-128); NT = N_bins_E + N_steps_z - 2 rows of the cross-section tables
+ * (nuSIprop.hpp:218-221).  Any pointer may be NULL. */
+int nusi_ctx_query(const nusi_ctx *c, int *N_bins_E, int *N_steps_z, int *NT, double *zmax_eff);
+/* get_energy(i) for all i (nuSIprop.hpp:412-429) plus the bin edges; each [N_bins_E] or NULL. */
+int nusi_ctx_energies(const nusi_ctx *c, double *Emin, double *Ecen, double *Emax);
+/* z[0..N_steps_z-1] (nuSIprop.hpp:125-127). */
+int nusi_ctx_redshifts(const nusi_ctx *c, double *z);
+/* |U_ab|^2, [3][3] row-major, a = flavour, b = mass (nuSIprop.hpp:155-163, used as std::norm). */
+int nusi_ctx_pmns2(const nusi_ctx *c, double *U2);
+/* The device-computed source term: out[(i-1)*N + j] = Lum(z[i], Emin[j], Emax[j]), i = 1..N_steps_z-1. */
+int nusi_ctx_source(const nusi_ctx *c, double *out);
+
+/* Neutrino masses for one mntot: nuSIaux::getmL + nuSIprop.hpp:184-203.  Host arithmetic.
+ * Returns NUSI_OK and mn[3], or NUSI_E_INVALID when the reference would exit(1). */
+int nusi_masses(double mntot, int normal_ordering, double mn[3]);
+
+/* evolve() for a batch of points (reference nuSIprop.hpp:176-337, called once per object).
+ * HOST buffers in, HOST buffers out; host<->device copies are inside the call.
+ *   mphi, g, mntot   [n]         the public members calculate_flux re-reads at each evolve() (:174)
+ *   flux_mass        [n][3][N]   get_flux(k, j)      (:359-381)   may be NULL
+ *   flux_fla         [n][3][N]   get_flux_fla(f, j)  (:383-405)   may be NULL
+ *   status           [n]         NUSI_ST_* bits, may be NULL
+ * si and norm do not enter: in this fork they only feed check_energy_conservation (:205). */
+int nusi_evolve_batch(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
+                      double *flux_mass, double *flux_fla, int *status);
+
+/* Device-resident variant: prepare once (host mass solve + upload), evolve many times with
+ * outputs left in HBM.  d_flux_mass / d_flux_fla / d_status are DEVICE pointers with the shapes
+ * above (either flux pointer may be NULL); stream is a cudaStream_t passed as void* (NULL =
+ * default stream).  The call only enqueues work. */
+int nusi_points_create(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
+                       nusi_points **out);
+void nusi_points_destroy(nusi_points *p);
+int nusi_points_count(const nusi_points *p);
+int nusi_evolve_points(nusi_ctx *c, const nusi_points *p, double *d_flux_mass, double *d_flux_fla,
+                       int *d_status, void *stream);
+
+/* The three cross-section tables of one evolve() (nuSIprop.hpp:218-253), computed by the CUDA
+ * builder, copied to HOST buffers.  Gamma, alphaTilde: [n][NT].  alpha: [n][NT][NT] dense
+ * row-major, entries m > i filled, others 0 (resonant-only contexts fill only m = i+1, the
+ * only entries that mode reads, nuSIprop.hpp:275).  Any pointer may be NULL. */
+int nusi_tables_batch(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
+                      double *Gamma, double *alphaTilde, double *alpha, int *status);
+
+/* CUDA-event time of the last evolve call on this context, per phase, summed over its launches:
+ * cross-section builder and z-stepping integrator [ms], and how many kernels were launched. */
+int nusi_last_timing(const nusi_ctx *c, float *ms_xsec, float *ms_integrate, int *n_launches);
+
+/* Device special functions evaluated on the GPU for n arguments (unit tests of the
+ * dilogarithms that replace gsl_sf_dilog / gsl_sf_complex_dilog_xy_e / polylogarithm::Li2,Li3).
+ * which: 0 Re Li2(x) ; 1 complex Li2(x + i y) -> (re, im) ; 2 Li2 on [-1,0] ; 3 Li3 on [-1,0]. */
+int nusi_specfun_eval(int device, int which, int n, const double *x, const double *y, double *re, double *im);
+
+/* Sustained FP64 FMA rate of the device [TFLOP/s] from a dependent-free DFMA loop (roofline
+ * denominator; MEASURED_PEAKS.json has no FP64 figure). */
+int nusi_measure_fp64_peak(int device, double *tflops);
+
+const char *nusi_strerror(int code);
+const char *nusi_last_error(void); /* text of the last CUDA/IO failure on this thread */
+int nusi_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NUSIPROP_B200_H */

@@ -1,0 +1,286 @@
+"""Host-side Python surface over the C ABI.
+
+`Context`   one (device, option set): the fixed constructor arguments of the reference's
+            nuSIprop::calculate_flux (reference nuSIprop.hpp:61-65) -- binning, zmax, ordering,
+            Majorana / non_resonant / phiphi switches, interacting flavour.
+`evolve_scan` / `Context.evolve` run calculate_flux::evolve() (nuSIprop.hpp:176-337) for a
+            whole batch of (mphi, g, mntot) points on the GPU.
+`pyprop`    drop-in mirror of the reference's Cython class (reference nuSIprop.pyx:12-144):
+            same constructor keywords and defaults, set_parameters, evolve, get_flux,
+            get_flux_fla, interp_flux_el/mu/ta, get_energies, check_energy_conservation.
+"""
+import ctypes as C
+import warnings
+
+import numpy as np
+
+from . import _lib
+from ._lib import NusiOpts, NusiError, c_double_p, c_int_p, check
+
+
+def _dp(a):
+    return a.ctypes.data_as(c_double_p) if a is not None else None
+
+
+def _ip(a):
+    return a.ctypes.data_as(c_int_p) if a is not None else None
+
+
+class Context(object):
+    """Grids, PMNS, source term and (optionally) phi-phi tables resident on one GPU."""
+
+    def __init__(self, majorana=True, non_resonant=True, normal_ordering=True, N_bins_E=300, lEmin=12.0,
+                 lEmax=17.0, zmax=5.0, flav=2, phiphi=False, device=0, alphatilde_phiphi_path=None,
+                 alpha_phiphi_path=None, max_points_per_launch=0):
+        self._lib = _lib.load()
+        o = NusiOpts()
+        check(self._lib.nusi_opts_default(C.byref(o)), "nusi_opts_default")
+        o.majorana, o.non_resonant, o.normal_ordering = int(bool(majorana)), int(bool(non_resonant)), int(bool(normal_ordering))
+        o.N_bins_E, o.lEmin, o.lEmax, o.zmax, o.flav, o.phiphi = int(N_bins_E), float(lEmin), float(lEmax), float(zmax), int(flav), int(bool(phiphi))
+        o.device = int(device)
+        o.max_points_per_launch = int(max_points_per_launch)
+        self._paths = (
+            alphatilde_phiphi_path.encode() if alphatilde_phiphi_path else None,
+            alpha_phiphi_path.encode() if alpha_phiphi_path else None,
+        )
+        o.alphatilde_phiphi_path, o.alpha_phiphi_path = self._paths
+        self._h = C.c_void_p()
+        check(self._lib.nusi_ctx_create(C.byref(self._h), C.byref(o)), "nusi_ctx_create")
+        n, nz, nt, zm = C.c_int(), C.c_int(), C.c_int(), C.c_double()
+        check(self._lib.nusi_ctx_query(self._h, C.byref(n), C.byref(nz), C.byref(nt), C.byref(zm)))
+        self.N_bins_E, self.N_steps_z, self.NT, self.zmax = n.value, nz.value, nt.value, zm.value
+        self.device = int(device)
+        self.opts = dict(majorana=bool(majorana), non_resonant=bool(non_resonant), normal_ordering=bool(normal_ordering),
+                         N_bins_E=int(N_bins_E), lEmin=float(lEmin), lEmax=float(lEmax), zmax=float(zmax), flav=int(flav),
+                         phiphi=bool(phiphi))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.nusi_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- grids -------------------------------------------------------------------------------
+    def energies(self):
+        """(Emin, Ecen, Emax), each [N_bins_E]; Ecen is what get_energy(i) returns."""
+        N = self.N_bins_E
+        a, b, c = np.zeros(N), np.zeros(N), np.zeros(N)
+        check(self._lib.nusi_ctx_energies(self._h, _dp(a), _dp(b), _dp(c)))
+        return a, b, c
+
+    def redshifts(self):
+        z = np.zeros(self.N_steps_z)
+        check(self._lib.nusi_ctx_redshifts(self._h, _dp(z)))
+        return z
+
+    def pmns2(self):
+        u = np.zeros(9)
+        check(self._lib.nusi_ctx_pmns2(self._h, _dp(u)))
+        return u.reshape(3, 3)
+
+    def source(self):
+        s = np.zeros((self.N_steps_z - 1, self.N_bins_E))
+        check(self._lib.nusi_ctx_source(self._h, _dp(s)))
+        return s
+
+    # ---- the hot path --------------------------------------------------------------------------
+    @staticmethod
+    def _points(mphi, g, mntot):
+        mphi, g, mntot = np.broadcast_arrays(np.atleast_1d(np.asarray(mphi, dtype=np.float64)),
+                                             np.atleast_1d(np.asarray(g, dtype=np.float64)),
+                                             np.atleast_1d(np.asarray(mntot, dtype=np.float64)))
+        return (np.ascontiguousarray(mphi), np.ascontiguousarray(g), np.ascontiguousarray(mntot))
+
+    def evolve(self, mphi, g, mntot, want_mass=True, want_flavour=True):
+        """Host arrays in, host arrays out: (flux_mass[n,3,N], flux_fla[n,3,N], status[n])."""
+        mphi, g, mntot = self._points(mphi, g, mntot)
+        n, N = mphi.size, self.N_bins_E
+        fm = np.empty((n, 3, N)) if want_mass else None
+        ff = np.empty((n, 3, N)) if want_flavour else None
+        st = np.zeros(n, dtype=np.int32)
+        check(self._lib.nusi_evolve_batch(self._h, n, _dp(mphi), _dp(g), _dp(mntot), _dp(fm), _dp(ff), _ip(st)), "nusi_evolve_batch")
+        return fm, ff, st
+
+    def tables(self, mphi, g, mntot, want_alpha=True):
+        """Cross-section tables (Gamma[n,NT], alphaTilde[n,NT], alpha[n,NT,NT], status[n])."""
+        mphi, g, mntot = self._points(mphi, g, mntot)
+        n, NT = mphi.size, self.NT
+        G, A = np.zeros((n, NT)), np.zeros((n, NT))
+        T = np.zeros((n, NT, NT)) if want_alpha else None
+        st = np.zeros(n, dtype=np.int32)
+        check(self._lib.nusi_tables_batch(self._h, n, _dp(mphi), _dp(g), _dp(mntot), _dp(G), _dp(A), _dp(T), _ip(st)), "nusi_tables_batch")
+        return G, A, T, st
+
+    def upload_points(self, mphi, g, mntot):
+        mphi, g, mntot = self._points(mphi, g, mntot)
+        return Points(self, mphi, g, mntot)
+
+    def evolve_points(self, pts, d_flux_mass=0, d_flux_fla=0, d_status=0, stream=0):
+        """Device-resident evolve: raw device addresses (ints), enqueue only."""
+        check(self._lib.nusi_evolve_points(self._h, pts._h, C.c_void_p(d_flux_mass or None), C.c_void_p(d_flux_fla or None),
+                                           C.c_void_p(d_status or None), C.c_void_p(stream or None)), "nusi_evolve_points")
+
+    def last_timing(self):
+        a, b, n = C.c_float(), C.c_float(), C.c_int()
+        check(self._lib.nusi_last_timing(self._h, C.byref(a), C.byref(b), C.byref(n)))
+        return dict(ms_xsec=a.value, ms_integrate=b.value, n_launches=n.value)
+
+
+class Points(object):
+    """A batch of prepared parameter points resident in HBM (nusi_points)."""
+
+    def __init__(self, ctx, mphi, g, mntot):
+        self._lib = ctx._lib
+        self._h = C.c_void_p()
+        self.n = int(mphi.size)
+        check(self._lib.nusi_points_create(ctx._h, self.n, _dp(mphi), _dp(g), _dp(mntot), C.byref(self._h)), "nusi_points_create")
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.nusi_points_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def masses(mntot, normal_ordering=True):
+    """Neutrino masses (m1, m2, m3) for a mass sum -- nuSIaux::getmL + nuSIprop.hpp:184-203."""
+    lib = _lib.load()
+    mn = np.zeros(3)
+    rc = lib.nusi_masses(float(mntot), int(bool(normal_ordering)), _dp(mn))
+    if rc != 0:
+        raise ValueError("No neutrino mass spectrum was found corresponding to \\sum m = %g" % mntot)
+    return mn
+
+
+def evolve_scan(mphi, g, mntot, **ctx_kwargs):
+    """One-call parameter scan: returns (flux_mass[n,3,N], flux_fla[n,3,N], status[n], energies[N])."""
+    ctx = Context(**ctx_kwargs)
+    try:
+        fm, ff, st = ctx.evolve(mphi, g, mntot)
+        return fm, ff, st, ctx.energies()[1]
+    finally:
+        ctx.close()
+
+
+def specfun(which, x, y=None, device=0):
+    """Device special functions (unit tests): 0 Re Li2, 1 complex Li2, 2 Li2 on [-1,0], 3 Li3 on [-1,0]."""
+    lib = _lib.load()
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    yy = np.ascontiguousarray(y, dtype=np.float64) if y is not None else None
+    re, im = np.zeros_like(x), np.zeros_like(x)
+    check(lib.nusi_specfun_eval(int(device), int(which), x.size, _dp(x), _dp(yy), _dp(re), _dp(im)), "nusi_specfun_eval")
+    return (re, im) if which == 1 else re
+
+
+def measure_fp64_peak(device=0):
+    lib = _lib.load()
+    t = C.c_double()
+    check(lib.nusi_measure_fp64_peak(int(device), C.byref(t)), "nusi_measure_fp64_peak")
+    return t.value
+
+
+class pyprop(object):
+    """Drop-in for the reference's Cython class `nuSIprop.pyprop` (reference nuSIprop.pyx:12-144).
+
+    Same constructor signature and defaults (note phiphi=True here vs False in C++,
+    nuSIprop.pyx:52), same methods.  evolve() runs on the GPU through the C ABI; contexts are
+    shared between objects with identical fixed options.
+    """
+
+    _ctx_cache = {}
+
+    def __init__(self, mphi, g, mntot, si, norm=1, majorana=True, non_resonant=True, normal_ordering=True,
+                 N_bins_E=300, lEmin=12.0, lEmax=17.0, zmax=5.0, flav=2, phiphi=True, device=0):
+        self.mphi, self.g, self.mntot, self.si, self.norm = float(mphi), float(g), float(mntot), float(si), float(norm)
+        key = (bool(majorana), bool(non_resonant), bool(normal_ordering), int(N_bins_E), float(lEmin), float(lEmax),
+               float(zmax), int(flav), bool(phiphi), int(device))
+        ctx = pyprop._ctx_cache.get(key)
+        if ctx is None:
+            ctx = Context(majorana=majorana, non_resonant=non_resonant, normal_ordering=normal_ordering, N_bins_E=N_bins_E,
+                          lEmin=lEmin, lEmax=lEmax, zmax=zmax, flav=flav, phiphi=phiphi, device=device)
+            pyprop._ctx_cache[key] = ctx
+        self._ctx = ctx
+        self.evolved = False
+        N = ctx.N_bins_E
+        self._flux = np.zeros((3, N))
+        self._flux_fla = np.zeros((3, N))
+        self.status = 0
+
+    def set_parameters(self, mphi=None, g=None, mntot=None, si=None, norm=None):
+        """Modify the physics parameters (reference nuSIprop.pyx:60-85)."""
+        if mphi is not None:
+            self.mphi = float(mphi)
+        if g is not None:
+            self.g = float(g)
+        if mntot is not None:
+            self.mntot = float(mntot)
+        if si is not None:
+            self.si = float(si)
+        if norm is not None:
+            self.norm = float(norm)
+        self.evolved = False
+
+    def evolve(self):
+        """Evolve the neutrino flux (reference nuSIprop.pyx:87-90)."""
+        self.evolved = True
+        fm, ff, st = self._ctx.evolve(self.mphi, self.g, self.mntot)
+        self.status = int(st[0])
+        if self.status & 256:
+            # the reference prints this and exit(1)s (aux.hpp:48-49); a library raises instead
+            raise ValueError("No neutrino mass spectrum was found corresponding to \\sum m = %g" % self.mntot)
+        self._flux, self._flux_fla = fm[0], ff[0]
+
+    def get_flux(self):
+        """Flux of each mass eigenstate [3, N_bins_E] (reference nuSIprop.pyx:92-104)."""
+        if not self.evolved:
+            warnings.warn("You have not evolved the neutrino flux! Zero flux will be returned.")
+            return np.zeros([3, self._ctx.N_bins_E])
+        return self._flux.copy()
+
+    def get_flux_fla(self):
+        """Flux of each flavour {e, mu, tau} [3, N_bins_E] (reference nuSIprop.pyx:106-118)."""
+        if not self.evolved:
+            warnings.warn("You have not evolved the neutrino flux! Zero flux will be returned.")
+            return np.zeros([3, self._ctx.N_bins_E])
+        return self._flux_fla.copy()
+
+    def _interp(self, f, energy):
+        import scipy.interpolate as interp
+        en = self.get_energies()
+        return interp.interp1d(np.log10(en), self.get_flux_fla()[f] * en ** self.si)(np.log10(energy)) / energy ** self.si
+
+    def interp_flux_el(self, energy):
+        return self._interp(0, energy)
+
+    def interp_flux_mu(self, energy):
+        return self._interp(1, energy)
+
+    def interp_flux_ta(self, energy):
+        return self._interp(2, energy)
+
+    def get_energies(self):
+        """Energy bin centers (reference nuSIprop.pyx:130-138)."""
+        return self._ctx.energies()[1].copy()
+
+    def check_energy_conservation(self):
+        """(E_int - E_FS)/E_FS with the reference's free-streaming integrals (nuSIprop.hpp:339-357,
+        666-744).  Host arithmetic on the GPU-evolved flux; like the reference it calls evolve()."""
+        from .freestream import energy_FS
+        E_FS = energy_FS(self._ctx, self.si, self.norm)
+        self.evolve()
+        Emin, Ecen, Emax = self._ctx.energies()
+        E_int = 0.0
+        for i in range(self._ctx.N_bins_E):
+            for k in range(3):
+                E_int += (np.log(Emax[i]) - np.log(Emin[i])) * Ecen[i] ** 2 * self._flux[k][i]
+        return (E_int - E_FS) / E_FS

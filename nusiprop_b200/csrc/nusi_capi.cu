@@ -1,0 +1,556 @@
+// nusi_capi.cu -- implementation of include/nusiprop_b200.h: contexts, batches of points, and the
+// launch sequence  rows_kernel + alpha_kernel (cross-section builder)  ->  integrate_kernel.
+// There is deliberately no host compute path in this library.
+#include "../../include/nusiprop_b200.h"
+#include "nusi_kernels.cuh"
+#include "nusi_host.hpp"
+
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstring>
+#include <array>
+#include <map>
+#include <string>
+#include <vector>
+#include <utility>
+
+using namespace nusi;
+
+static thread_local std::string g_last_error;
+static int fail(int code, const std::string &msg) {
+  g_last_error = msg;
+  return code;
+}
+#define CU(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess)                                                                         \
+      return fail(NUSI_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));                \
+  } while (0)
+
+template <typename T>
+static cudaError_t upload(const std::vector<T> &h, T **d) {
+  cudaError_t e = cudaMalloc((void **)d, h.size() * sizeof(T) + 8);
+  if (e != cudaSuccess) return e;
+  return cudaMemcpy(*d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+struct nusi_ctx {
+  nusi_opts opt;
+  HostGrid H;
+  DeviceGrid G;
+  // device arrays owned by the context
+  double *d_row_lo = nullptr, *d_row_hi = nullptr, *d_dE = nullptr, *d_cz = nullptr, *d_ndz = nullptr;
+  double *d_source = nullptr, *d_Emin = nullptr, *d_Emax = nullptr, *d_zsrc = nullptr, *d_rsn = nullptr;
+  double *d_pp[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  // per-launch work space (grown on demand)
+  int cap_points = 0;
+  size_t tstride = 0;
+  double *d_rows = nullptr, *d_tri = nullptr, *d_work = nullptr;
+  int max_chunk = 0;
+  // timing of the last evolve call
+  std::vector<cudaEvent_t> ev;  // triples: start, after xsec, after integrate
+  int ev_used = 0;
+  int n_launches = 0;
+  std::map<std::pair<double, int>, std::pair<bool, std::array<double, 3>>> mass_cache;
+};
+
+struct nusi_points {
+  int n = 0;
+  int device = 0;
+  PointParams *d_params = nullptr;
+  int *d_status0 = nullptr;  // host-side status (NO_MASS) pre-uploaded, OR'ed into the outputs
+  std::vector<int> h_status0;
+};
+
+extern "C" {
+
+int nusi_abi_version(void) { return NUSI_ABI_VERSION; }
+const char *nusi_last_error(void) { return g_last_error.c_str(); }
+const char *nusi_strerror(int code) {
+  switch (code) {
+    case NUSI_OK: return "ok";
+    case NUSI_E_INVALID: return "invalid argument";
+    case NUSI_E_NO_DEVICE: return "no usable CUDA device (this library has no CPU path)";
+    case NUSI_E_CUDA: return "CUDA runtime error";
+    case NUSI_E_TABLE: return "phi-phi table file missing or malformed";
+    case NUSI_E_NOMEM: return "out of memory";
+    default: return "unknown error";
+  }
+}
+
+int nusi_opts_default(nusi_opts *o) {
+  if (!o) return NUSI_E_INVALID;
+  std::memset(o, 0, sizeof(*o));
+  o->majorana = 1;
+  o->non_resonant = 1;
+  o->normal_ordering = 1;
+  o->N_bins_E = 300;
+  o->lEmin = 12.0;
+  o->lEmax = 17.0;
+  o->zmax = 5.0;
+  o->flav = 2;
+  o->phiphi = 0;
+  o->device = 0;
+  return NUSI_OK;
+}
+
+int nusi_masses(double mntot, int normal_ordering, double mn[3]) {
+  if (!mn) return NUSI_E_INVALID;
+  return solve_masses(mntot, normal_ordering != 0, mn) ? NUSI_OK : NUSI_E_INVALID;
+}
+
+void nusi_ctx_destroy(nusi_ctx *c) {
+  if (!c) return;
+  cudaSetDevice(c->opt.device);
+  double *ptrs[] = {c->d_row_lo, c->d_row_hi, c->d_dE, c->d_cz, c->d_ndz, c->d_source, c->d_Emin, c->d_Emax,
+                    c->d_zsrc, c->d_rsn, c->d_pp[0], c->d_pp[1], c->d_pp[2], c->d_pp[3], c->d_pp[4],
+                    c->d_rows, c->d_tri, c->d_work};
+  for (double *p : ptrs)
+    if (p) cudaFree(p);
+  for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
+  delete c;
+}
+
+int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
+  if (!out || !o) return NUSI_E_INVALID;
+  *out = nullptr;
+  if (o->N_bins_E < 2 || !(o->lEmax > o->lEmin) || !(o->zmax > 0) || o->flav < 0 || o->flav > 2)
+    return fail(NUSI_E_INVALID, "bad binning / flavour options");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || o->device < 0 || o->device >= ndev)
+    return fail(NUSI_E_NO_DEVICE, "no CUDA device with the requested ordinal");
+  CU(cudaSetDevice(o->device));
+
+  nusi_ctx *c = new nusi_ctx;
+  c->opt = *o;
+  build_grid(o->N_bins_E, o->lEmin, o->lEmax, o->zmax, o->normal_ordering != 0, c->H);
+  const HostGrid &H = c->H;
+  if (H.Nz < 2) {
+    delete c;
+    return fail(NUSI_E_INVALID, "zmax too small for this binning (fewer than 2 redshift steps)");
+  }
+#define UP(vec, ptr)                                                            \
+  do {                                                                          \
+    cudaError_t e_ = upload(vec, &ptr);                                         \
+    if (e_ != cudaSuccess) {                                                    \
+      nusi_ctx_destroy(c);                                                      \
+      return fail(NUSI_E_CUDA, std::string("upload: ") + cudaGetErrorString(e_)); \
+    }                                                                           \
+  } while (0)
+  UP(H.row_lo, c->d_row_lo);
+  UP(H.row_hi, c->d_row_hi);
+  UP(H.dE, c->d_dE);
+  UP(H.cz, c->d_cz);
+  UP(H.ndz, c->d_ndz);
+  UP(H.Emin, c->d_Emin);
+  UP(H.Emax, c->d_Emax);
+  UP(H.zsrc, c->d_zsrc);
+  UP(H.rsn, c->d_rsn);
+
+  DeviceGrid &G = c->G;
+  std::memset(&G, 0, sizeof(G));
+  G.N = H.N;
+  G.Nz = H.Nz;
+  G.NT = H.NT;
+  G.majorana = o->majorana != 0;
+  G.non_resonant = o->non_resonant != 0;
+  G.phiphi = (o->phiphi != 0) && (o->non_resonant != 0);  // tables are loaded only then (nuSIprop.hpp:166)
+  G.flav = o->flav;
+  G.row_lo = c->d_row_lo;
+  G.row_hi = c->d_row_hi;
+  G.dE = c->d_dE;
+  G.cz = c->d_cz;
+  G.ndz = c->d_ndz;
+  for (int i = 0; i < 9; ++i) G.U2[i] = H.U2[i];
+
+  if (G.phiphi) {
+    HostPhiPhi T;
+    const char *p_at = o->alphatilde_phiphi_path ? o->alphatilde_phiphi_path : "xsec/alphatilde_phiphi.bin";
+    const char *p_a = o->alpha_phiphi_path ? o->alpha_phiphi_path : "xsec/alpha_phiphi.bin";
+    const std::string err = load_phiphi(p_at, p_a, std::log10(H.Emax[0] / H.Emin[0]), T);
+    if (!err.empty()) {
+      nusi_ctx_destroy(c);
+      return fail(NUSI_E_TABLE, err);
+    }
+    UP(T.at_x0, c->d_pp[0]);
+    UP(T.at_f, c->d_pp[1]);
+    UP(T.a_x0, c->d_pp[2]);
+    UP(T.a_x1, c->d_pp[3]);
+    UP(T.a_f, c->d_pp[4]);
+    G.pp.at_n0 = (int)T.at_x0.size();
+    G.pp.at_x0 = c->d_pp[0];
+    G.pp.at_f = c->d_pp[1];
+    G.pp.a_n0 = (int)T.a_x0.size();
+    G.pp.a_n1 = (int)T.a_x1.size();
+    G.pp.a_x0 = c->d_pp[2];
+    G.pp.a_x1 = c->d_pp[3];
+    G.pp.a_f = c->d_pp[4];
+    G.pp.delta_in_range = T.delta_in_range;
+  }
+#undef UP
+
+  // source term, once per context, on the device
+  const int S = H.Nz - 1;
+  cudaError_t e = cudaMalloc((void **)&c->d_source, (size_t)S * H.N * sizeof(double));
+  if (e == cudaSuccess) {
+    source_kernel<<<(S * H.N + 127) / 128, 128>>>(H.N, S, c->d_zsrc, c->d_rsn, H.lum_pref, c->d_Emin, c->d_Emax,
+                                                  c->d_source);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  }
+  if (e != cudaSuccess) {
+    nusi_ctx_destroy(c);
+    return fail(NUSI_E_CUDA, std::string("source_kernel: ") + cudaGetErrorString(e));
+  }
+  G.source = c->d_source;
+
+  c->tstride = G.non_resonant ? (size_t)H.NT * (H.NT - 1) / 2 : (size_t)H.NT;
+  // chunk size: keep the packed tables of one launch within ~1/4 of free HBM, at most 8192 points
+  size_t free_b = 0, total_b = 0;
+  cudaMemGetInfo(&free_b, &total_b);
+  const size_t per_point = (c->tstride + 2 * (size_t)H.NT + 3 * (size_t)H.N) * sizeof(double);
+  size_t chunk = (free_b / 4) / per_point;
+  if (chunk > 8192) chunk = 8192;
+  if (chunk < 1) chunk = 1;
+  if (o->max_points_per_launch > 0 && (size_t)o->max_points_per_launch < chunk) chunk = o->max_points_per_launch;
+  c->max_chunk = (int)chunk;
+  *out = c;
+  return NUSI_OK;
+}
+
+int nusi_ctx_query(const nusi_ctx *c, int *N, int *Nz, int *NT, double *zmax_eff) {
+  if (!c) return NUSI_E_INVALID;
+  if (N) *N = c->H.N;
+  if (Nz) *Nz = c->H.Nz;
+  if (NT) *NT = c->H.NT;
+  if (zmax_eff) *zmax_eff = c->H.zmax_eff;
+  return NUSI_OK;
+}
+int nusi_ctx_energies(const nusi_ctx *c, double *Emin, double *Ecen, double *Emax) {
+  if (!c) return NUSI_E_INVALID;
+  const size_t b = c->H.N * sizeof(double);
+  if (Emin) std::memcpy(Emin, c->H.Emin.data(), b);
+  if (Ecen) std::memcpy(Ecen, c->H.Ecen.data(), b);
+  if (Emax) std::memcpy(Emax, c->H.Emax.data(), b);
+  return NUSI_OK;
+}
+int nusi_ctx_redshifts(const nusi_ctx *c, double *z) {
+  if (!c || !z) return NUSI_E_INVALID;
+  std::memcpy(z, c->H.z.data(), c->H.Nz * sizeof(double));
+  return NUSI_OK;
+}
+int nusi_ctx_pmns2(const nusi_ctx *c, double *U2) {
+  if (!c || !U2) return NUSI_E_INVALID;
+  std::memcpy(U2, c->H.U2, 9 * sizeof(double));
+  return NUSI_OK;
+}
+int nusi_ctx_source(const nusi_ctx *c, double *out) {
+  if (!c || !out) return NUSI_E_INVALID;
+  CU(cudaSetDevice(c->opt.device));
+  CU(cudaMemcpy(out, c->d_source, (size_t)(c->H.Nz - 1) * c->H.N * sizeof(double), cudaMemcpyDeviceToHost));
+  return NUSI_OK;
+}
+
+// host preparation of a batch: masses (cached per mntot), width, |U_fk|^2
+static void prepare_points(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
+                           std::vector<PointParams> &pp, std::vector<int> &st) {
+  pp.resize(n);
+  st.assign(n, 0);
+  const bool no = c->opt.normal_ordering != 0;
+  for (int i = 0; i < n; ++i) {
+    PointParams &P = pp[i];
+    std::memset(&P, 0, sizeof(P));
+    auto key = std::make_pair(mntot[i], (int)no);
+    auto it = c->mass_cache.find(key);
+    if (it == c->mass_cache.end()) {
+      std::array<double, 3> m = {0, 0, 0};
+      const bool ok = solve_masses(mntot[i], no, m.data());
+      it = c->mass_cache.emplace(key, std::make_pair(ok, m)).first;
+    }
+    P.majorana = c->G.majorana;
+    P.non_resonant = c->G.non_resonant;
+    P.phiphi = c->G.phiphi;
+    if (!it->second.first || !(mphi[i] > 0)) {
+      st[i] = NUSI_ST_NO_MASS;
+      P.mphi = -1.0;  // kernels skip the point and write NaN
+      continue;
+    }
+    P.mphi = mphi[i];
+    P.g = g[i];
+    P.Ga = scalar_width(mphi[i], g[i], c->G.majorana != 0);
+    for (int k = 0; k < 3; ++k) {
+      P.mn[k] = it->second.second[k];
+      P.U2f[k] = c->H.U2[c->opt.flav * 3 + k];
+    }
+  }
+}
+
+static int ensure_workspace(nusi_ctx *c, int npts) {
+  if (npts <= c->cap_points) return NUSI_OK;
+  if (c->d_rows) cudaFree(c->d_rows);
+  if (c->d_tri) cudaFree(c->d_tri);
+  if (c->d_work) cudaFree(c->d_work);
+  c->d_rows = c->d_tri = c->d_work = nullptr;
+  c->cap_points = 0;
+  CU(cudaMalloc((void **)&c->d_rows, (size_t)npts * 2 * c->H.NT * sizeof(double)));
+  CU(cudaMalloc((void **)&c->d_tri, (size_t)npts * c->tstride * sizeof(double)));
+  if (!c->G.non_resonant) CU(cudaMalloc((void **)&c->d_work, (size_t)npts * 3 * c->H.N * sizeof(double)));
+  c->cap_points = npts;
+  return NUSI_OK;
+}
+
+static int next_events(nusi_ctx *c, cudaEvent_t **e3) {
+  if ((int)c->ev.size() < c->ev_used + 3) {
+    for (int i = 0; i < 3; ++i) {
+      cudaEvent_t e;
+      CU(cudaEventCreate(&e));
+      c->ev.push_back(e);
+    }
+  }
+  *e3 = &c->ev[c->ev_used];
+  c->ev_used += 3;
+  return NUSI_OK;
+}
+
+// enqueue the cross-section builder for `cnt` points starting at params
+static int launch_xsec(nusi_ctx *c, const PointParams *d_params, int cnt, int *d_status, cudaStream_t s) {
+  const DeviceGrid &G = c->G;
+  dim3 gr((G.NT + 127) / 128, cnt);
+  rows_kernel<<<gr, 128, 0, s>>>(G, d_params, c->d_rows, d_status);
+  const long long nent = G.non_resonant ? (long long)G.NT * (G.NT - 1) / 2 : (long long)(G.NT - 1);
+  dim3 ga((unsigned)((nent + 127) / 128), cnt);
+  alpha_kernel<<<ga, 128, 0, s>>>(G, d_params, c->d_tri, c->tstride, d_status);
+  c->n_launches += 2;
+  CU(cudaGetLastError());
+  return NUSI_OK;
+}
+
+static int launch_integrate(nusi_ctx *c, const PointParams *d_params, int cnt, double *d_fm, double *d_ff,
+                            cudaStream_t s) {
+  const DeviceGrid &G = c->G;
+  if (G.non_resonant) {
+    const int N = G.N;
+    int thr = 256;
+    if (N <= 256) thr = ((N + 31) / 32) * 32;
+    if (N <= thr)
+      integrate_kernel<1><<<cnt, thr, 0, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff);
+    else if (N <= 2 * 256)
+      integrate_kernel<2><<<cnt, 256, 0, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff);
+    else if (N <= 4 * 256)
+      integrate_kernel<4><<<cnt, 256, 0, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff);
+    else if (N <= 8 * 256)
+      integrate_kernel<8><<<cnt, 256, 0, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff);
+    else if (N <= 16 * 256)
+      integrate_kernel<16><<<cnt, 256, 0, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff);
+    else
+      return fail(NUSI_E_INVALID, "N_bins_E > 4096 is not supported by the integrator");
+  } else {
+    integrate_resonant_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(G, cnt, d_params, c->d_rows, c->d_tri, c->tstride,
+                                                             c->d_work, d_fm, d_ff);
+  }
+  c->n_launches += 1;
+  CU(cudaGetLastError());
+  return NUSI_OK;
+}
+
+int nusi_points_create(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
+                       nusi_points **out) {
+  if (!c || !out || n <= 0 || !mphi || !g || !mntot) return NUSI_E_INVALID;
+  CU(cudaSetDevice(c->opt.device));
+  std::vector<PointParams> pp;
+  nusi_points *p = new nusi_points;
+  p->n = n;
+  p->device = c->opt.device;
+  prepare_points(c, n, mphi, g, mntot, pp, p->h_status0);
+  cudaError_t e = cudaMalloc((void **)&p->d_params, (size_t)n * sizeof(PointParams));
+  if (e == cudaSuccess) e = cudaMalloc((void **)&p->d_status0, (size_t)n * sizeof(int));
+  if (e == cudaSuccess) e = cudaMemcpy(p->d_params, pp.data(), (size_t)n * sizeof(PointParams), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(p->d_status0, p->h_status0.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    nusi_points_destroy(p);
+    return fail(NUSI_E_CUDA, std::string("points upload: ") + cudaGetErrorString(e));
+  }
+  *out = p;
+  return NUSI_OK;
+}
+void nusi_points_destroy(nusi_points *p) {
+  if (!p) return;
+  cudaSetDevice(p->device);
+  if (p->d_params) cudaFree(p->d_params);
+  if (p->d_status0) cudaFree(p->d_status0);
+  delete p;
+}
+int nusi_points_count(const nusi_points *p) { return p ? p->n : 0; }
+
+int nusi_evolve_points(nusi_ctx *c, const nusi_points *p, double *d_fm, double *d_ff, int *d_status, void *stream) {
+  if (!c || !p) return NUSI_E_INVALID;
+  CU(cudaSetDevice(c->opt.device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const int N = c->H.N;
+  const int chunk = p->n < c->max_chunk ? p->n : c->max_chunk;
+  int rc = ensure_workspace(c, chunk);
+  if (rc) return rc;
+  c->ev_used = 0;
+  c->n_launches = 0;
+  int *d_st = d_status ? d_status : p->d_status0;
+  if (d_status) CU(cudaMemcpyAsync(d_status, p->d_status0, (size_t)p->n * sizeof(int), cudaMemcpyDeviceToDevice, s));
+  for (int off = 0; off < p->n; off += chunk) {
+    const int cnt = (p->n - off < chunk) ? p->n - off : chunk;
+    cudaEvent_t *e3;
+    if ((rc = next_events(c, &e3))) return rc;
+    CU(cudaEventRecord(e3[0], s));
+    if ((rc = launch_xsec(c, p->d_params + off, cnt, d_st + off, s))) return rc;
+    CU(cudaEventRecord(e3[1], s));
+    double *fm = d_fm ? d_fm + (size_t)off * 3 * N : nullptr;
+    double *ff = d_ff ? d_ff + (size_t)off * 3 * N : nullptr;
+    if ((rc = launch_integrate(c, p->d_params + off, cnt, fm, ff, s))) return rc;
+    CU(cudaEventRecord(e3[2], s));
+  }
+  return NUSI_OK;
+}
+
+int nusi_evolve_batch(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
+                      double *flux_mass, double *flux_fla, int *status) {
+  if (!c || n <= 0 || !mphi || !g || !mntot) return NUSI_E_INVALID;
+  nusi_points *p = nullptr;
+  int rc = nusi_points_create(c, n, mphi, g, mntot, &p);
+  if (rc) return rc;
+  const size_t fb = (size_t)n * 3 * c->H.N * sizeof(double);
+  double *d_fm = nullptr, *d_ff = nullptr;
+  int *d_st = nullptr;
+  cudaError_t e = cudaSuccess;
+  if (flux_mass) e = cudaMalloc((void **)&d_fm, fb);
+  if (e == cudaSuccess && flux_fla) e = cudaMalloc((void **)&d_ff, fb);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&d_st, (size_t)n * sizeof(int));
+  if (e == cudaSuccess) {
+    rc = nusi_evolve_points(c, p, d_fm, d_ff, d_st, nullptr);
+    if (rc == NUSI_OK) {
+      if (flux_mass) e = cudaMemcpy(flux_mass, d_fm, fb, cudaMemcpyDeviceToHost);
+      if (e == cudaSuccess && flux_fla) e = cudaMemcpy(flux_fla, d_ff, fb, cudaMemcpyDeviceToHost);
+      if (e == cudaSuccess && status) e = cudaMemcpy(status, d_st, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost);
+      if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    }
+  }
+  if (d_fm) cudaFree(d_fm);
+  if (d_ff) cudaFree(d_ff);
+  if (d_st) cudaFree(d_st);
+  nusi_points_destroy(p);
+  if (rc) return rc;
+  if (e != cudaSuccess) return fail(NUSI_E_CUDA, std::string("evolve_batch: ") + cudaGetErrorString(e));
+  return NUSI_OK;
+}
+
+int nusi_tables_batch(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot, double *Gamma,
+                      double *alphaTilde, double *alpha, int *status) {
+  if (!c || n <= 0 || !mphi || !g || !mntot) return NUSI_E_INVALID;
+  CU(cudaSetDevice(c->opt.device));
+  const int NT = c->H.NT;
+  nusi_points *p = nullptr;
+  int rc = nusi_points_create(c, n, mphi, g, mntot, &p);
+  if (rc) return rc;
+  c->ev_used = 0;
+  c->n_launches = 0;
+  std::vector<double> hrows((size_t)2 * NT), htri(c->tstride);
+  for (int i = 0; i < n && rc == NUSI_OK; ++i) {
+    rc = ensure_workspace(c, 1);
+    if (rc) break;
+    rc = launch_xsec(c, p->d_params + i, 1, p->d_status0 + i, nullptr);
+    if (rc) break;
+    cudaError_t e = cudaMemcpy(hrows.data(), c->d_rows, hrows.size() * sizeof(double), cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(htri.data(), c->d_tri, htri.size() * sizeof(double), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) {
+      rc = fail(NUSI_E_CUDA, std::string("tables_batch: ") + cudaGetErrorString(e));
+      break;
+    }
+    if (Gamma) std::memcpy(Gamma + (size_t)i * NT, hrows.data(), NT * sizeof(double));
+    if (alphaTilde) std::memcpy(alphaTilde + (size_t)i * NT, hrows.data() + NT, NT * sizeof(double));
+    if (alpha) {
+      double *A = alpha + (size_t)i * NT * NT;
+      std::memset(A, 0, (size_t)NT * NT * sizeof(double));
+      if (c->G.non_resonant) {
+        for (int b = 1; b < NT; ++b)
+          for (int a = 0; a < b; ++a) A[(size_t)a * NT + b] = htri[(size_t)b * (b - 1) / 2 + a];
+      } else {
+        for (int a = 0; a + 1 < NT; ++a) A[(size_t)a * NT + a + 1] = htri[a];
+      }
+    }
+  }
+  if (rc == NUSI_OK && status) {
+    cudaError_t e = cudaMemcpy(status, p->d_status0, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) rc = fail(NUSI_E_CUDA, cudaGetErrorString(e));
+  }
+  nusi_points_destroy(p);
+  return rc;
+}
+
+int nusi_last_timing(const nusi_ctx *c, float *ms_xsec, float *ms_integrate, int *n_launches) {
+  if (!c) return NUSI_E_INVALID;
+  float tx = 0, ti = 0;
+  for (int i = 0; i + 2 < c->ev_used + 0 && i + 2 < (int)c->ev.size(); i += 3) {
+    CU(cudaEventSynchronize(c->ev[i + 2]));
+    float a = 0, b = 0;
+    CU(cudaEventElapsedTime(&a, c->ev[i], c->ev[i + 1]));
+    CU(cudaEventElapsedTime(&b, c->ev[i + 1], c->ev[i + 2]));
+    tx += a;
+    ti += b;
+  }
+  if (ms_xsec) *ms_xsec = tx;
+  if (ms_integrate) *ms_integrate = ti;
+  if (n_launches) *n_launches = c->n_launches;
+  return NUSI_OK;
+}
+
+int nusi_specfun_eval(int device, int which, int n, const double *x, const double *y, double *re, double *im) {
+  if (n <= 0 || !x || !re || which < 0 || which > 3 || (which == 1 && (!y || !im))) return NUSI_E_INVALID;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+    return fail(NUSI_E_NO_DEVICE, "no CUDA device");
+  CU(cudaSetDevice(device));
+  double *d[4] = {nullptr, nullptr, nullptr, nullptr};
+  const size_t b = (size_t)n * sizeof(double);
+  for (int i = 0; i < 4; ++i) CU(cudaMalloc((void **)&d[i], b));
+  CU(cudaMemcpy(d[0], x, b, cudaMemcpyHostToDevice));
+  if (y) CU(cudaMemcpy(d[1], y, b, cudaMemcpyHostToDevice));
+  specfun_kernel<<<(n + 127) / 128, 128>>>(which, n, d[0], d[1], d[2], d[3]);
+  CU(cudaGetLastError());
+  CU(cudaMemcpy(re, d[2], b, cudaMemcpyDeviceToHost));
+  if (im && which == 1) CU(cudaMemcpy(im, d[3], b, cudaMemcpyDeviceToHost));
+  for (int i = 0; i < 4; ++i) cudaFree(d[i]);
+  return NUSI_OK;
+}
+
+int nusi_measure_fp64_peak(int device, double *tflops) {
+  if (!tflops) return NUSI_E_INVALID;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+    return fail(NUSI_E_NO_DEVICE, "no CUDA device");
+  CU(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  const int blocks = prop.multiProcessorCount * 8, thr = 256, iters = 1 << 15;
+  double *d = nullptr;
+  CU(cudaMalloc((void **)&d, (size_t)blocks * thr * sizeof(double)));
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0));
+  CU(cudaEventCreate(&e1));
+  double best = 0;
+  for (int rep = 0; rep < 4; ++rep) {
+    CU(cudaEventRecord(e0));
+    fp64_peak_kernel<<<blocks, thr>>>(d, iters, 0.999999, 1e-9);
+    CU(cudaEventRecord(e1));
+    CU(cudaEventSynchronize(e1));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    const double fl = 2.0 * 8.0 * (double)iters * blocks * thr;
+    const double tf = fl / (ms * 1e-3) / 1e12;
+    if (rep > 0 && tf > best) best = tf;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d);
+  *tflops = best;
+  return NUSI_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,289 @@
+// nusi_host.cpp -- see nusi_host.hpp.  Compiled with -ffp-contract=off so every expression
+// rounds exactly as written (the oracle build uses the same flag).
+#include "nusi_host.hpp"
+#include "nusi_interp.h"
+#include <cmath>
+#include <complex>
+#include <cstdio>
+#include <cstring>
+
+namespace nusi {
+
+static double cosmo_nd(double z) { return 4.3528e-13 * cub(1 + z); }                              // nuSIprop.hpp:573-580
+static double cosmo_H(double z) { return 1.5e-33 * std::pow(0.692 + 0.308 * cub(1 + z), 0.5); }   // :582-589
+static double cosmo_SFR(double z) {                                                                // :591-605
+  return std::pow(std::pow(1 + z, -3.4 * 10) + std::pow((1 + z) / 5161, 0.3 * 10) + std::pow((1 + z) / 9.06, 3.5 * 10),
+                  -1. / 10.);
+}
+static double cosmo_RSN(double z) {  // :607-616
+  const double m_solar = 1.989 * 56.1;
+  return cosmo_SFR(z) * 0.01 / (m_solar);
+}
+
+void build_grid(int N, double lEmin, double lEmax, double zmax, bool normal_ordering, HostGrid &G) {
+  G.N = N;
+  G.Emin.resize(N);
+  G.Ecen.resize(N);
+  G.Emax.resize(N);
+  G.dE.resize(N);
+  for (int i = 0; i < N; ++i) {
+    G.Emin[i] = std::pow(10, lEmin + (lEmax - lEmin) * (i * 1.0) / N);
+    G.Ecen[i] = std::pow(10, lEmin + (lEmax - lEmin) * (i + 0.5) / N);
+    G.Emax[i] = std::pow(10, lEmin + (lEmax - lEmin) * (i + 1.0) / N);
+    G.dE[i] = G.Emax[i] - G.Emin[i];
+  }
+  // redshift step = energy step (nuSIprop.hpp:120-128); the (int) truncation is the reference's
+  G.Nz = (int)(std::log((1 + zmax) / (1 + 0)) / std::log(G.Emax[0] / G.Emin[0]) + 2);
+  G.z.resize(G.Nz);
+  for (int i = 0; i < G.Nz; ++i) G.z[i] = (1 + 0) * std::pow(G.Emax[0] / G.Emin[0], i) - 1;
+  G.zmax_eff = G.z[G.Nz - 1];
+  G.NT = N + G.Nz - 2;
+
+  G.row_lo.resize(G.NT);
+  G.row_hi.resize(G.NT);
+  for (int i = 0; i < G.NT; ++i) {
+    if (i < N) {
+      G.row_lo[i] = G.Emin[i];
+      G.row_hi[i] = G.Emax[i];
+    } else {  // top bin blue-shifted to higher redshift
+      G.row_lo[i] = G.Emin[N - 1] * (1 + G.z[i - N + 1]);
+      G.row_hi[i] = G.Emax[N - 1] * (1 + G.z[i - N + 1]);
+    }
+  }
+
+  const double dlogz = std::log(1 + G.z[1]) - std::log(1 + G.z[0]);
+  const int S = G.Nz - 1;
+  G.cz.resize(S);
+  G.ndz.resize(S);
+  G.rsn.resize(S);
+  G.zsrc.resize(S);
+  for (int i = 1; i < G.Nz; ++i) {
+    const double zr = G.z[i - 1];
+    G.cz[i - 1] = (1 + zr) * dlogz / cosmo_H(zr);
+    G.ndz[i - 1] = cosmo_nd(zr) / sqr(1 + zr);
+    G.rsn[i - 1] = cosmo_RSN(G.z[i]);
+    G.zsrc[i - 1] = G.z[i];
+  }
+  {
+    const double Etot = 3 * 6.24, Tnue = 6e6;
+    G.lum_pref = (Etot * 120 / (6 * 7 * std::pow(M_PI, 4) * std::pow(Tnue, 2)));
+  }
+
+  // NuFIT 5.0 mixing (nuSIprop.hpp:130-163); only |U|^2 is ever used
+  double t12, t13, t23, dcp;
+  if (normal_ordering) {
+    t12 = 33.44 * (M_PI / 180);
+    t13 = 8.57 * (M_PI / 180);
+    t23 = 49.0 * (M_PI / 180);
+    dcp = 195.0 * (M_PI / 180);
+  } else {
+    t12 = 33.45 * (M_PI / 180);
+    t13 = 8.61 * (M_PI / 180);
+    t23 = 49.3 * (M_PI / 180);
+    dcp = 286.0 * (M_PI / 180);
+  }
+  const double c12 = std::cos(t12), c13 = std::cos(t13), c23 = std::cos(t23);
+  const double s12 = std::sin(t12), s13 = std::sin(t13), s23 = std::sin(t23);
+  const std::complex<double> del(std::cos(dcp), std::sin(dcp));
+  std::complex<double> U[3][3];
+  U[0][0] = c12 * c13;
+  U[0][1] = s12 * c13;
+  U[0][2] = s13 * 1.0 / del;
+  U[1][0] = -s12 * c23 - c12 * s23 * s13 * del;
+  U[1][1] = c12 * c23 - s12 * s23 * s13 * del;
+  U[1][2] = s23 * c13;
+  U[2][0] = s12 * s23 - c12 * c23 * s13 * del;
+  U[2][1] = -c12 * s23 - s12 * c23 * s13 * del;
+  U[2][2] = c23 * c13;
+  for (int a = 0; a < 3; ++a)
+    for (int b = 0; b < 3; ++b) G.U2[a * 3 + b] = std::norm(U[a][b]);
+}
+
+double scalar_width(double mphi, double g, bool majorana) {
+  if (majorana) return sqr(g) * mphi / (16.0 * M_PI);
+  return sqr(g) * mphi / (8.0 * M_PI);
+}
+
+// Roots of a quartic by simultaneous (Durand-Kerner) iteration in long double.  The reference
+// uses gsl_poly_complex_solve (aux.hpp:34-36); any solver works because getmL accepts at most
+// one root for physical inputs -- what matters is the acceptance test below.
+static void quartic_roots(const double a[5], double out_re[4], double out_im[4]) {
+  typedef std::complex<long double> C;
+  const int deg = 4;
+  C r[4];
+  long double scale = 0;
+  for (int i = 0; i < deg; ++i) {
+    long double v = std::pow(std::fabs((long double)a[i] / (long double)a[deg]), 1.0L / (deg - i));
+    if (v > scale) scale = v;
+  }
+  if (scale == 0) scale = 1;
+  for (int i = 0; i < deg; ++i) r[i] = scale * std::pow(C(0.4L, 0.9L), i);
+  for (int it = 0; it < 2000; ++it) {
+    long double mv = 0;
+    for (int i = 0; i < deg; ++i) {
+      C p = (long double)a[deg];
+      for (int k = deg - 1; k >= 0; --k) p = p * r[i] + (long double)a[k];
+      C d = (long double)a[deg];
+      for (int j = 0; j < deg; ++j)
+        if (j != i) d *= (r[i] - r[j]);
+      const C step = p / d;
+      r[i] -= step;
+      const long double m = std::abs(step);
+      if (m > mv) mv = m;
+    }
+    if (mv < 1e-30L * scale) break;
+  }
+  for (int i = 0; i < deg; ++i) {
+    out_re[i] = (double)r[i].real();
+    out_im[i] = (double)r[i].imag();
+  }
+}
+
+bool solve_masses(double mSum, bool normal_ordering, double mn[3]) {
+  const double dmqSL = 7.42e-5;
+  const double dmqAT = normal_ordering ? 2.514e-3 : -2.497e-3;
+  double coeff[5];
+  if (dmqAT > 0) {
+    coeff[0] = -(sqr(sqr(mSum)) - 2 * sqr(mSum) * (dmqSL + dmqAT) + sqr(dmqSL - dmqAT));
+    coeff[1] = 4 * mSum * (sqr(mSum) - dmqSL - dmqAT);
+    coeff[2] = -2 * (sqr(mSum) - dmqSL - dmqAT);
+    coeff[3] = -4 * mSum;
+    coeff[4] = 3;
+  } else {
+    coeff[0] = -(sqr(sqr(mSum)) - 2 * sqr(mSum) * (-dmqSL - 2 * dmqAT) + sqr(dmqSL));
+    coeff[1] = 4 * mSum * (sqr(mSum) + dmqSL + 2 * dmqAT);
+    coeff[2] = -2 * (sqr(mSum) + dmqSL + 2 * dmqAT);
+    coeff[3] = -4 * mSum;
+    coeff[4] = 3;
+  }
+  double re[4], im[4];
+  quartic_roots(coeff, re, im);
+  double mL = 0;
+  bool found = false;
+  for (int i = 0; i < 4 && !found; ++i) {
+    const double ml = re[i];
+    if ((im[i] < 1.0e-7) && (ml >= 0) && (mSum - ml > 1.0e-7) &&
+        ((dmqAT > 0 && (sqr(mSum) - dmqAT - dmqSL - sqr(ml) - 2 * ml * mSum > 1.0e-7)) ||
+         (dmqAT < 0 && (sqr(mSum) + 2 * dmqAT + dmqSL - sqr(ml) - 2 * ml * mSum > 1.0e-7)))) {
+      mL = ml;
+      found = true;
+    }
+  }
+  if (!found) return false;
+  if (normal_ordering) {
+    mn[0] = mL;
+    mn[1] = std::sqrt(dmqSL + sqr(mL));
+    mn[2] = std::sqrt(dmqAT + sqr(mL));
+  } else {
+    mn[2] = mL;
+    mn[1] = std::sqrt(sqr(mL) - dmqAT);
+    mn[0] = std::sqrt(sqr(mn[1]) - dmqSL);
+  }
+  return true;
+}
+
+// ---------------------------------------------------------------------------------------
+// phi-phi tables
+// ---------------------------------------------------------------------------------------
+static bool read_floats(const char *path, std::vector<float> &buf, std::string &err) {
+  FILE *fp = std::fopen(path, "rb");
+  if (!fp) {
+    err = std::string("Error at interp: the input file ") + path + " does not exist";
+    return false;
+  }
+  std::fseek(fp, 0, SEEK_END);
+  const long sz = std::ftell(fp);
+  std::fseek(fp, 0, SEEK_SET);
+  buf.resize((size_t)sz / sizeof(float));
+  const size_t got = std::fread(buf.data(), sizeof(float), buf.size(), fp);
+  std::fclose(fp);
+  if (got != buf.size()) {
+    err = std::string("short read on ") + path;
+    return false;
+  }
+  return true;
+}
+
+// Records are (x_0, ..., x_{D-1}, f) float32 with the LAST coordinate running fastest
+// (interp.hpp:259-290).  The reference hard-codes the node counts (5000x100, 1000x1000x100);
+// here they are recovered from the coordinate columns so that smaller tables of the same
+// format also load.
+static bool infer_dims(const std::vector<float> &buf, int D, int dims[3], std::string &err) {
+  const size_t rec = (size_t)D + 1, nrec = buf.size() / rec;
+  if (nrec == 0 || buf.size() % rec) {
+    err = "phi-phi table: file size is not a whole number of records";
+    return false;
+  }
+  size_t stride = 1;
+  for (int ax = D - 1; ax >= 0; --ax) {
+    size_t cnt = 1;
+    while (cnt * stride < nrec && buf[(cnt * stride) * rec + ax] != buf[ax]) ++cnt;
+    if (ax == 0) cnt = nrec / stride;
+    dims[ax] = (int)cnt;
+    stride *= cnt;
+  }
+  if (stride != nrec) {
+    err = "phi-phi table: could not recover the node grid";
+    return false;
+  }
+  return true;
+}
+
+std::string load_phiphi(const char *at_path, const char *a_path, double l10d, HostPhiPhi &T) {
+  std::string err;
+  std::vector<float> buf;
+  // ---- alphaTilde: (|tbar+|, log10 delta, f)
+  if (!read_floats(at_path, buf, err)) return err;
+  int d2[3] = {0, 0, 0};
+  if (!infer_dims(buf, 2, d2, err)) return err;
+  {
+    const int n0 = d2[0], n1 = d2[1];
+    if (n0 < 4 || n1 < 4) return "phi-phi alphaTilde table: too few nodes";
+    std::vector<double> x1(n1);
+    for (int c = 0; c < n1; ++c) x1[c] = (double)buf[(size_t)c * 3 + 1];
+    T.delta_in_range = interp_inside(x1.data(), n1, l10d) ? 1 : 0;
+    T.at_x0.resize(n0);
+    T.at_f.assign(n0, 0.0);
+    for (int a = 0; a < n0; ++a) T.at_x0[a] = std::log((double)buf[((size_t)a * n1) * 3 + 0]);
+    if (T.delta_in_range) {
+      AxisStencil S;
+      interp_axis(x1.data(), n1, l10d, S);
+      for (int a = 0; a < n0; ++a) {
+        double acc = 0;
+        for (int c = 0; c < S.cnt; ++c) acc += (double)buf[((size_t)a * n1 + S.i0 + c) * 3 + 2] * S.c[c];
+        T.at_f[a] = acc;
+      }
+    }
+  }
+  // ---- alpha: (sbar, n, log10 delta, f)
+  if (!read_floats(a_path, buf, err)) return err;
+  int d3[3] = {0, 0, 0};
+  if (!infer_dims(buf, 3, d3, err)) return err;
+  {
+    const int n0 = d3[0], n1 = d3[1], n2 = d3[2];
+    if (n0 < 4 || n1 < 4 || n2 < 4) return "phi-phi alpha table: too few nodes";
+    std::vector<double> x2(n2);
+    for (int c = 0; c < n2; ++c) x2[c] = (double)buf[(size_t)c * 4 + 2];
+    const int in2 = interp_inside(x2.data(), n2, l10d) ? 1 : 0;
+    T.delta_in_range = T.delta_in_range && in2;
+    T.a_x0.resize(n0);
+    T.a_x1.resize(n1);
+    T.a_f.assign((size_t)n0 * n1, 0.0);
+    for (int a = 0; a < n0; ++a) T.a_x0[a] = std::log((double)buf[((size_t)a * n1 * n2) * 4 + 0]);
+    for (int b = 0; b < n1; ++b) T.a_x1[b] = (double)buf[((size_t)b * n2) * 4 + 1];
+    if (in2) {
+      AxisStencil S;
+      interp_axis(x2.data(), n2, l10d, S);
+      for (int a = 0; a < n0; ++a)
+        for (int b = 0; b < n1; ++b) {
+          double acc = 0;
+          for (int c = 0; c < S.cnt; ++c)
+            acc += (double)buf[(((size_t)a * n1 + b) * n2 + S.i0 + c) * 4 + 3] * S.c[c];
+          T.a_f[(size_t)a * n1 + b] = acc;
+        }
+    }
+  }
+  return "";
+}
+
+}  // namespace nusi
