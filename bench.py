@@ -1,0 +1,339 @@
+#!/usr/bin/env python
+"""bench.py -- the reference's headline metric on B200: (mphi, g) evolutions per second at N_E = 200.
+
+Workload (BASELINE.json configs[4], SURVEY 8(d) "S-scan"): the 256 x 256 parameter scan
+    mphi_i = 10^(1 + 3 i/255) eV,  g_j = 10^(-5 + 5 j/255),  mntot = 0.1 eV,
+    Majorana, non_resonant, normal ordering, N_bins_E = 200, lE 4 -> 9, zmax = 5, flav = 2, phiphi off
+sharded statically over the 8 GPUs of a box: scan point p belongs to shard p mod 8.  One "step" is
+one evolve() of every point of a shard (8192 points) per GPU: with --gpus 8 a step is the whole
+scan, with fewer GPUs it is the first N shards (weak scaling, fixed per-GPU work).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's own CPU evolve()
+
+One JSON line on stdout (rank 0).  `value` times the device-resident path (inputs already in HBM,
+outputs left in HBM); `e2e` times nusi_evolve_batch through the C ABI with HOST buffers (H2D of
+the parameters and D2H of both flux arrays inside the timed region).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np
+
+N_E, LEMIN, LEMAX, ZMAX, FLAV = 200, 4.0, 9.0, 5.0, 2
+MNTOT = 0.1
+N_SHARDS = 8
+# algorithmic FP64 work (add/mul/div = 1, FMA = 2, log/exp = 32, atan = 48, Li2 = 96,
+# complex Li2 = 320) after common-subexpression elimination
+KFLOP_ALPHA_ENTRY = 13.9e3
+KFLOP_ROW = 22.4e3
+FLOP_LUMINT = 308.0
+
+
+def scan_points():
+    i, j = np.meshgrid(np.arange(256), np.arange(256), indexing="ij")
+    mphi = 10.0 ** (1.0 + 3.0 * i / 255.0)
+    g = 10.0 ** (-5.0 + 5.0 * j / 255.0)
+    return mphi.ravel(), g.ravel()
+
+
+def shard(rank):
+    mphi, g = scan_points()
+    idx = np.arange(rank, mphi.size, N_SHARDS)
+    return np.ascontiguousarray(mphi[idx]), np.ascontiguousarray(g[idx])
+
+
+def flops_per_evolution(NT, N, Nz):
+    table = NT * (NT - 1) / 2 * KFLOP_ALPHA_ENTRY
+    rows = NT * KFLOP_ROW
+    integ = (Nz - 1) * (N * (N - 1) + 90.0 * N)
+    return table, rows, integ
+
+
+class ClockSampler(object):
+    """nvidia-smi clock / throttle-reason samples DURING the timed region (profiling recipe)."""
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU reference arm: the reference's own evolve() (oracle/_ref = unmodified headers + refshim),
+# one process per parameter point, all host cores
+# ---------------------------------------------------------------------------------------------
+def ref_binary():
+    for name in ("nusi_ref_o3", "nusi_ref"):
+        p = os.path.join(ROOT, "oracle", "_ref", name)
+        if os.path.exists(p):
+            return p
+    return None
+
+
+def run_reference_sample(points, cores):
+    """Run evolve() for `points` [(mphi, g)] with `cores` concurrent single-point processes.
+    Returns wall seconds."""
+    exe = ref_binary()
+    if exe is None:
+        raise RuntimeError("oracle/_ref/nusi_ref_o3 missing (build it with `make -C oracle` where /root/reference exists)")
+    it = iter(points)
+    lock = threading.Lock()
+
+    def worker():
+        while True:
+            with lock:
+                try:
+                    mphi, g = next(it)
+                except StopIteration:
+                    return
+            subprocess.run([exe, "evolve", repr(float(mphi)), repr(float(g)), repr(MNTOT), "2", "1", "1", "1", "1", str(N_E),
+                            repr(LEMIN), repr(LEMAX), repr(ZMAX), str(FLAV), "0", "1", "1"],
+                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, check=True)
+
+    t0 = time.perf_counter()
+    th = [threading.Thread(target=worker) for _ in range(cores)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    return time.perf_counter() - t0
+
+
+def cpu_sample_points(count):
+    """Seeded subsample of the scan (default_rng(20261104).choice(65536, 1024))."""
+    mphi, g = scan_points()
+    idx = np.random.default_rng(20261104).choice(mphi.size, 1024, replace=False)[:count]
+    return [(mphi[i], g[i]) for i in idx]
+
+
+def bench_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cores = os.cpu_count() or 1
+    per_step = max(cores * 2, 16)  # ~2 evolve() per core per step, ~0.35 s each
+    for _ in range(args.warmup):
+        run_reference_sample(cpu_sample_points(min(cores, 16)), cores)
+    t = 0.0
+    for s in range(args.steps):
+        t += run_reference_sample(cpu_sample_points(per_step), cores)
+    value = per_step * args.steps / t
+    sample = "%d evolve() per step (seeded subsample of the 256x256 scan), one process per point, %d concurrent" % (per_step, cores)
+    line = {
+        "metric": "(mphi,g) evolutions/sec at N_E=200", "value": value, "unit": "evolutions/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "impl": "reference",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": value, "unit": "evolutions/s", "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": value, "unit": "evolutions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(gpus):
+    return {"workload": "S-scan: 256x256 (mphi,g) grid, shard p mod 8 per GPU (8192 points per GPU per step), N_E=200, lE 4->9, "
+                        "zmax=5, Majorana, non_resonant, NO, flav=2, phiphi off, mntot=0.1",
+            "points_per_gpu_per_step": 8192, "N_bins_E": N_E, "parallelism": "points sharded over %d GPU(s), gather to rank 0" % gpus,
+            "l2": "per-step working set (packed alpha tables, 1.7 GB per GPU) exceeds the 126 MB L2; no flush needed"}
+
+
+# ---------------------------------------------------------------------------------------------
+# CUDA arm
+# ---------------------------------------------------------------------------------------------
+def bench_cuda(args):
+    import torch
+    import torch.distributed as dist
+    import nusiprop_b200 as nb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+
+    ctx = nb.Context(majorana=True, non_resonant=True, normal_ordering=True, N_bins_E=N_E, lEmin=LEMIN, lEmax=LEMAX, zmax=ZMAX,
+                     flav=FLAV, phiphi=False, device=local)
+    mphi, g = shard(rank % N_SHARDS)
+    if args.points:
+        mphi, g = mphi[: args.points], g[: args.points]
+    n = mphi.size
+    mntot = np.full(n, MNTOT)
+    pts = ctx.upload_points(mphi, g, mntot)
+    fm = torch.empty((n, 3, N_E), dtype=torch.float64, device=dev)
+    ff = torch.empty_like(fm)
+    st = torch.zeros(n, dtype=torch.int32, device=dev)
+    gathered = [torch.empty_like(ff) for _ in range(world)] if (world > 1 and rank == 0) else None
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        ctx.evolve_points(pts, fm.data_ptr(), ff.data_ptr(), st.data_ptr(), stream)
+        if world > 1:  # the scan's only exchange: final gather of the flavour fluxes to rank 0
+            dist.gather(ff, gathered, dst=0)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 0)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_rows = t_alpha = t_int = 0.0
+    launches = 0
+    e0.record()
+    for _ in range(args.steps):
+        step()
+        tm = ctx.last_timing()  # blocks on this step's events (no effect on device time)
+        t_rows += tm["ms_rows"]
+        t_alpha += tm["ms_alpha"]
+        t_int += tm["ms_integrate"]
+        launches += tm["n_launches"]
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    clocks = sampler.stop() if rank == 0 else None
+
+    # end-to-end through the C ABI with host buffers (pinned), every rank concurrently
+    h_fm = torch.empty((n, 3, N_E), dtype=torch.float64, pin_memory=True).numpy()
+    h_ff = torch.empty((n, 3, N_E), dtype=torch.float64, pin_memory=True).numpy()
+    from nusiprop_b200.api import _dp, _ip
+    h_st = np.zeros(n, dtype=np.int32)
+    lib = ctx._lib
+
+    def e2e_step():
+        rc = lib.nusi_evolve_batch(ctx._h, n, _dp(mphi), _dp(g), _dp(mntot), _dp(h_fm), _dp(h_ff), _ip(h_st))
+        if rc != 0:
+            raise RuntimeError("nusi_evolve_batch rc=%d" % rc)
+
+    e2e_steps = max(1, min(args.steps, 3))
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    # the device path and the host path must agree bit for bit
+    same = bool(np.array_equal(ff.cpu().numpy(), h_ff, equal_nan=True))
+
+    if rank == 0:
+        N, Nz, NT = ctx.N_bins_E, ctx.N_steps_z, ctx.NT
+        f_tab, f_rows, f_int = flops_per_evolution(NT, N, Nz)
+        total_ev = n * world * args.steps
+        value = total_ev / (ms * 1e-3)
+        peak = nb.measure_fp64_peak(local)
+        ach_alpha = (f_tab * n * args.steps) / (t_alpha * 1e-3) / 1e12 if t_alpha > 0 else None
+        line = {
+            "metric": "(mphi,g) evolutions/sec at N_E=200", "value": value, "unit": "evolutions/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(world),
+            "us_per_z_step": 1e3 * t_int / (n * args.steps * (Nz - 1)),
+            "kernel_ms_per_step": {"rows_kernel": t_rows / args.steps, "alpha_kernel": t_alpha / args.steps, "integrate_kernel": t_int / args.steps},
+            "roofline": {"bound": "fp64", "kernel": "alpha_kernel", "achieved": ach_alpha, "peak": peak, "unit": "TFLOP/s",
+                         "frac": (ach_alpha / peak) if ach_alpha else None, "traffic": None,
+                         "note": "peak = DFMA rate measured in this run by nusi_measure_fp64_peak (MEASURED_PEAKS.json has no FP64 figure); "
+                                 "achieved = 13.9 kflop x NT(NT-1)/2 entries x points per launch / CUDA-event time of the kernel"},
+            "e2e": {"value": n * world * e2e_steps / e2e_s, "unit": "evolutions/s", "h2d_bytes_per_step": int(3 * 8 * n),
+                    "d2h_bytes_per_step": int(2 * 3 * N * 8 * n + 4 * n), "bitwise_equal_to_device_path": same},
+            "gpu_launches": launches,
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            cnt = max(cores * 32, 32)
+            try:
+                wall = run_reference_sample(cpu_sample_points(cnt), cores)
+                line["cpu_baseline"] = {"value": cnt / wall, "unit": "evolutions/s", "cores": cores, "kind": "reference",
+                                        "sample": "%d evolve() of the seeded scan subsample, one process per point, %d concurrent, %.1f s" % (cnt, cores, wall)}
+            except Exception as ex:  # oracle binary absent
+                line["cpu_baseline"] = {"value": None, "unit": "evolutions/s", "cores": cores, "kind": "reference", "sample": "unavailable: %s" % ex}
+        print(json.dumps(line))
+    pts.close()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
+    ap.add_argument("--points", type=int, default=0, help="debug: evolve only the first POINTS points of the shard")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return bench_reference(args)
+    return bench_cuda(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -113,9 +113,10 @@ int nusi_evolve_points(nusi_ctx *c, const nusi_points *p, double *d_flux_mass, d
 int nusi_tables_batch(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
                       double *Gamma, double *alphaTilde, double *alpha, int *status);
 
-/* CUDA-event time of the last evolve call on this context, per phase, summed over its launches:
- * cross-section builder and z-stepping integrator [ms], and how many kernels were launched. */
-int nusi_last_timing(const nusi_ctx *c, float *ms_xsec, float *ms_integrate, int *n_launches);
+/* CUDA-event time of the last nusi_evolve_points / nusi_evolve_batch on this context, per kernel,
+ * summed over its launches [ms]: Gamma/alphaTilde rows, alpha table, z-stepping integrator; and
+ * how many kernels were launched.  Blocks until that work has finished. */
+int nusi_last_timing(const nusi_ctx *c, float *ms_rows, float *ms_alpha, float *ms_integrate, int *n_launches);
 
 /* Device special functions evaluated on the GPU for n arguments (unit tests of the
  * dilogarithms that replace gsl_sf_dilog / gsl_sf_complex_dilog_xy_e / polylogarithm::Li2,Li3).

@@ -49,7 +49,7 @@ SIGNATURES = {
     "nusi_points_count": (C.c_int, [C.c_void_p]),
     "nusi_evolve_points": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "nusi_tables_batch": (C.c_int, [C.c_void_p, C.c_int, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_int_p]),
-    "nusi_last_timing": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float), c_int_p]),
+    "nusi_last_timing": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), c_int_p]),
     "nusi_specfun_eval": (C.c_int, [C.c_int, C.c_int, C.c_int, c_double_p, c_double_p, c_double_p, c_double_p]),
     "nusi_measure_fp64_peak": (C.c_int, [C.c_int, c_double_p]),
 }

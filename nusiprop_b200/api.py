@@ -126,9 +126,9 @@ class Context(object):
                                            C.c_void_p(d_status or None), C.c_void_p(stream or None)), "nusi_evolve_points")
 
     def last_timing(self):
-        a, b, n = C.c_float(), C.c_float(), C.c_int()
-        check(self._lib.nusi_last_timing(self._h, C.byref(a), C.byref(b), C.byref(n)))
-        return dict(ms_xsec=a.value, ms_integrate=b.value, n_launches=n.value)
+        r, a, b, n = C.c_float(), C.c_float(), C.c_float(), C.c_int()
+        check(self._lib.nusi_last_timing(self._h, C.byref(r), C.byref(a), C.byref(b), C.byref(n)))
+        return dict(ms_rows=r.value, ms_alpha=a.value, ms_integrate=b.value, n_launches=n.value)
 
 
 class Points(object):

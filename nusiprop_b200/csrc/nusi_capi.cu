@@ -49,7 +49,7 @@ struct nusi_ctx {
   double *d_rows = nullptr, *d_tri = nullptr, *d_work = nullptr;
   int max_chunk = 0;
   // timing of the last evolve call
-  std::vector<cudaEvent_t> ev;  // triples: start, after xsec, after integrate
+  std::vector<cudaEvent_t> ev;  // quadruples: start, after rows_kernel, after alpha_kernel, after integrate
   int ev_used = 0;
   int n_launches = 0;
   std::map<std::pair<double, int>, std::pair<bool, std::array<double, 3>>> mass_cache;
@@ -301,23 +301,25 @@ static int ensure_workspace(nusi_ctx *c, int npts) {
 }
 
 static int next_events(nusi_ctx *c, cudaEvent_t **e3) {
-  if ((int)c->ev.size() < c->ev_used + 3) {
-    for (int i = 0; i < 3; ++i) {
+  if ((int)c->ev.size() < c->ev_used + 4) {
+    for (int i = 0; i < 4; ++i) {
       cudaEvent_t e;
       CU(cudaEventCreate(&e));
       c->ev.push_back(e);
     }
   }
   *e3 = &c->ev[c->ev_used];
-  c->ev_used += 3;
+  c->ev_used += 4;
   return NUSI_OK;
 }
 
 // enqueue the cross-section builder for `cnt` points starting at params
-static int launch_xsec(nusi_ctx *c, const PointParams *d_params, int cnt, int *d_status, cudaStream_t s) {
+static int launch_xsec(nusi_ctx *c, const PointParams *d_params, int cnt, int *d_status, cudaStream_t s,
+                       cudaEvent_t mid = nullptr) {
   const DeviceGrid &G = c->G;
   dim3 gr((G.NT + 127) / 128, cnt);
   rows_kernel<<<gr, 128, 0, s>>>(G, d_params, c->d_rows, d_status);
+  if (mid) CU(cudaEventRecord(mid, s));
   const long long nent = G.non_resonant ? (long long)G.NT * (G.NT - 1) / 2 : (long long)(G.NT - 1);
   dim3 ga((unsigned)((nent + 127) / 128), cnt);
   alpha_kernel<<<ga, 128, 0, s>>>(G, d_params, c->d_tri, c->tstride, d_status);
@@ -400,12 +402,12 @@ int nusi_evolve_points(nusi_ctx *c, const nusi_points *p, double *d_fm, double *
     cudaEvent_t *e3;
     if ((rc = next_events(c, &e3))) return rc;
     CU(cudaEventRecord(e3[0], s));
-    if ((rc = launch_xsec(c, p->d_params + off, cnt, d_st + off, s))) return rc;
-    CU(cudaEventRecord(e3[1], s));
+    if ((rc = launch_xsec(c, p->d_params + off, cnt, d_st + off, s, e3[1]))) return rc;
+    CU(cudaEventRecord(e3[2], s));
     double *fm = d_fm ? d_fm + (size_t)off * 3 * N : nullptr;
     double *ff = d_ff ? d_ff + (size_t)off * 3 * N : nullptr;
     if ((rc = launch_integrate(c, p->d_params + off, cnt, fm, ff, s))) return rc;
-    CU(cudaEventRecord(e3[2], s));
+    CU(cudaEventRecord(e3[3], s));
   }
   return NUSI_OK;
 }
@@ -484,18 +486,21 @@ int nusi_tables_batch(nusi_ctx *c, int n, const double *mphi, const double *g, c
   return rc;
 }
 
-int nusi_last_timing(const nusi_ctx *c, float *ms_xsec, float *ms_integrate, int *n_launches) {
+int nusi_last_timing(const nusi_ctx *c, float *ms_rows, float *ms_alpha, float *ms_integrate, int *n_launches) {
   if (!c) return NUSI_E_INVALID;
-  float tx = 0, ti = 0;
-  for (int i = 0; i + 2 < c->ev_used + 0 && i + 2 < (int)c->ev.size(); i += 3) {
-    CU(cudaEventSynchronize(c->ev[i + 2]));
-    float a = 0, b = 0;
+  float tr = 0, ta = 0, ti = 0;
+  for (int i = 0; i + 3 < c->ev_used + 0 && i + 3 < (int)c->ev.size(); i += 4) {
+    CU(cudaEventSynchronize(c->ev[i + 3]));
+    float a = 0, b = 0, d = 0;
     CU(cudaEventElapsedTime(&a, c->ev[i], c->ev[i + 1]));
     CU(cudaEventElapsedTime(&b, c->ev[i + 1], c->ev[i + 2]));
-    tx += a;
-    ti += b;
+    CU(cudaEventElapsedTime(&d, c->ev[i + 2], c->ev[i + 3]));
+    tr += a;
+    ta += b;
+    ti += d;
   }
-  if (ms_xsec) *ms_xsec = tx;
+  if (ms_rows) *ms_rows = tr;
+  if (ms_alpha) *ms_alpha = ta;
   if (ms_integrate) *ms_integrate = ti;
   if (n_launches) *n_launches = c->n_launches;
   return NUSI_OK;
