@@ -7,6 +7,7 @@
 
 #include <cuda_runtime.h>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <array>
 #include <map>
@@ -43,6 +44,10 @@ struct nusi_ctx {
   double *d_row_lo = nullptr, *d_row_hi = nullptr, *d_dE = nullptr, *d_cz = nullptr, *d_ndz = nullptr;
   double *d_source = nullptr, *d_Emin = nullptr, *d_Emax = nullptr, *d_zsrc = nullptr, *d_rsn = nullptr;
   double *d_pp[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  double *d_edgeE = nullptr;  // distinct bin-edge energies of the table cells (tiled builder)
+  int2 *d_tiles = nullptr;
+  int n_tiles = 0;
+  bool use_tiles = false;
   // per-launch work space (grown on demand)
   int cap_points = 0;
   size_t tstride = 0;
@@ -105,7 +110,8 @@ void nusi_ctx_destroy(nusi_ctx *c) {
   cudaSetDevice(c->opt.device);
   double *ptrs[] = {c->d_row_lo, c->d_row_hi, c->d_dE, c->d_cz, c->d_ndz, c->d_source, c->d_Emin, c->d_Emax,
                     c->d_zsrc, c->d_rsn, c->d_pp[0], c->d_pp[1], c->d_pp[2], c->d_pp[3], c->d_pp[4],
-                    c->d_rows, c->d_tri, c->d_work};
+                    c->d_rows, c->d_tri, c->d_work, c->d_edgeE};
+  if (c->d_tiles) cudaFree(c->d_tiles);
   for (double *p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
@@ -205,6 +211,34 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
   }
   G.source = c->d_source;
 
+  // tiled builder (Majorana + non-resonant): edge list with shared main-grid edges
+  if (G.non_resonant && G.majorana && !getenv("NUSI_NO_TILES")) {
+    bool shared_ok = true;
+    for (int a = 0; a + 1 < H.N; ++a) shared_ok = shared_ok && (H.row_hi[a] == H.row_lo[a + 1]);
+    if (shared_ok) {
+      std::vector<double> edge((size_t)H.N + 1 + 2 * (H.NT - H.N));
+      for (int a = 0; a < H.N; ++a) edge[a] = H.row_lo[a];
+      edge[H.N] = H.row_hi[H.N - 1];
+      for (int a = H.N; a < H.NT; ++a) {
+        edge[H.N + 1 + 2 * (a - H.N)] = H.row_lo[a];
+        edge[H.N + 2 + 2 * (a - H.N)] = H.row_hi[a];
+      }
+      std::vector<int2> tiles;
+      const int nt = (H.NT + NUSI_TS - 1) / NUSI_TS;
+      for (int tb = 0; tb < nt; ++tb)
+        for (int ta = 0; ta <= tb; ++ta) tiles.push_back(make_int2(ta, tb));
+      cudaError_t e1 = upload(edge, &c->d_edgeE);
+      if (e1 == cudaSuccess) e1 = upload(tiles, &c->d_tiles);
+      if (e1 == cudaSuccess)
+        e1 = cudaFuncSetAttribute(alpha_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem));
+      if (e1 != cudaSuccess) {
+        nusi_ctx_destroy(c);
+        return fail(NUSI_E_CUDA, std::string("tile setup: ") + cudaGetErrorString(e1));
+      }
+      c->n_tiles = (int)tiles.size();
+      c->use_tiles = true;
+    }
+  }
   c->tstride = G.non_resonant ? (size_t)H.NT * (H.NT - 1) / 2 : (size_t)H.NT;
   // chunk size: keep the packed tables of one launch within ~1/4 of free HBM, at most 8192 points
   size_t free_b = 0, total_b = 0;
@@ -320,9 +354,14 @@ static int launch_xsec(nusi_ctx *c, const PointParams *d_params, int cnt, int *d
   dim3 gr((G.NT + 127) / 128, cnt);
   rows_kernel<<<gr, 128, 0, s>>>(G, d_params, c->d_rows, d_status);
   if (mid) CU(cudaEventRecord(mid, s));
-  const long long nent = G.non_resonant ? (long long)G.NT * (G.NT - 1) / 2 : (long long)(G.NT - 1);
-  dim3 ga((unsigned)((nent + 127) / 128), cnt);
-  alpha_kernel<<<ga, 128, 0, s>>>(G, d_params, c->d_tri, c->tstride, d_status);
+  if (c->use_tiles) {
+    dim3 gt(c->n_tiles, cnt);
+    alpha_tile_kernel<<<gt, 256, sizeof(TileSmem), s>>>(G, d_params, c->d_edgeE, c->d_tiles, c->d_tri, c->tstride, d_status);
+  } else {
+    const long long nent = G.non_resonant ? (long long)G.NT * (G.NT - 1) / 2 : (long long)(G.NT - 1);
+    dim3 ga((unsigned)((nent + 127) / 128), cnt);
+    alpha_kernel<<<ga, 128, 0, s>>>(G, d_params, c->d_tri, c->tstride, d_status);
+  }
   c->n_launches += 2;
   CU(cudaGetLastError());
   return NUSI_OK;
