@@ -66,9 +66,12 @@ NUSI_HD double atilde_dilog_combi(double tminus, double tplus) {
          li2_real(1 + (1 + tminus - tplus) / tplus) - li2_real(1 + 1 / tplus);
 }
 
-// adds target mass k's contribution to the running total of alphaTilde(Em, Ep)
-NUSI_HD void alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k, double Em, double Ep,
-                             double &tot, int *warn) {
+// Channel contributions of target mass k to alphaTilde(Em, Ep) in the reference's order of
+// accumulation: ch[0..6] = s, t, u, tu, st, su, phiphi (weighted with mphi^4/(2 m_k)); returns
+// how many are filled (1 for resonant-only).
+#define NUSI_ATILDE_NCH 7
+NUSI_HD int alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k, double Em, double Ep,
+                            double *ch, int *warn) {
   const double mphi = P.mphi, g = P.g, Ga = P.Ga;
   const double g4 = sqr(sqr(g)), m4 = sqr(sqr(mphi));
   const double U2 = P.U2f[k];
@@ -96,8 +99,8 @@ NUSI_HD void alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k
   }
   As *= U2;
   if (!P.majorana) As /= 2.;
-  tot += wgt * As;
-  if (!P.non_resonant) return;
+  ch[0] = wgt * As;
+  if (!P.non_resonant) return 1;
 
   const double lm = log1p(-tminus), lp = log1p(-tplus);  // ln(1-t-), ln(1-t+)
   const double ld = log1p(tminus - tplus);               // ln(1 + t- - t+)
@@ -121,8 +124,8 @@ NUSI_HD void alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k
     if (Au < 0) Au = atilde_gl2d<1>(tplus, tminus) * (1. / 2. * g4 / (32 * kPi * m4));
     Au *= U2;
   }
-  tot += wgt * At;
-  tot += wgt * Au;
+  ch[1] = wgt * At;
+  ch[2] = wgt * Au;
 
   /* t-u interference (Majorana only) */
   double Atu;
@@ -140,7 +143,7 @@ NUSI_HD void alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k
     Atu = 0;
   }
   Atu *= U2;
-  tot += wgt * Atu;
+  ch[3] = wgt * Atu;
 
   /* s-t interference */
   const double gr = Ga / mphi;
@@ -199,11 +202,11 @@ NUSI_HD void alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k
            (1 + tminus + sqr(gr)) * (lam_p - lam_m));
   }
   Ast *= U2;
-  tot += wgt * Ast;
+  ch[4] = wgt * Ast;
 
   /* s-u interference: Majorana only */
   const double Asu = P.majorana ? Ast : 0.0;
-  tot += wgt * Asu;
+  ch[5] = wgt * Asu;
 
   /* double-scalar production: table lookup inside 4 < -t+ < 1e4, asymptotic form above */
   double App = 0;
@@ -224,17 +227,22 @@ NUSI_HD void alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k
     App *= 2;
     if (P.majorana) App *= 2;
   }
-  tot += wgt * App;
+  ch[6] = wgt * App;
 
   const double nrm = sqr(sqr(g / mphi));
   if (warn && (As < 0 || At < 0 || Au < 0 || Atu / nrm < -1e-11 || (Ast + At + As) / nrm < -1e-11 ||
                (Asu + Au + As) / nrm < -1e-11))
     *warn |= 2;
+  return NUSI_ATILDE_NCH;
 }
 
 NUSI_HD double alphatilde_row(const PointParams &P, const PhiPhiTables *pp, double Em, double Ep, int *warn) {
   double tot = 0;
-  for (int k = 0; k < 3; ++k) alphatilde_mass(P, pp, k, Em, Ep, tot, warn);
+  for (int k = 0; k < 3; ++k) {
+    double ch[NUSI_ATILDE_NCH];
+    const int n = alphatilde_mass(P, pp, k, Em, Ep, ch, warn);
+    for (int c = 0; c < n; ++c) tot += ch[c];
+  }
   return tot;
 }
 

@@ -101,7 +101,7 @@ NUSI_HD cplx dilog_cplx_large(cplx z) {
   const cplx cont = mk(-0.5 * inner.im, 0.5 * inner.re);
   return -(1.0 / (16. * (z2 * z2))) - 1.0 / (9. * (z2 * z)) - 1.0 / (4. * z2) - 1.0 / z - cont;
 }
-NUSI_HD cplx dilogdiff_complex(cplx x, cplx y) {
+NUSI_HD_NOINLINE cplx dilogdiff_complex(cplx x, cplx y) {
   if (cabs_(x) > 1e2 && cabs_(y) > 1e2) return dilog_cplx_large(x) - dilog_cplx_large(y);
   return cli2(x.re, x.im) - cli2(y.re, y.im);
 }

@@ -351,8 +351,8 @@ static int next_events(nusi_ctx *c, cudaEvent_t **e3) {
 static int launch_xsec(nusi_ctx *c, const PointParams *d_params, int cnt, int *d_status, cudaStream_t s,
                        cudaEvent_t mid = nullptr) {
   const DeviceGrid &G = c->G;
-  dim3 gr((G.NT + 127) / 128, cnt);
-  rows_kernel<<<gr, 128, 0, s>>>(G, d_params, c->d_rows, d_status);
+  dim3 gr((G.NT + NUSI_ROWS_PER_CTA - 1) / NUSI_ROWS_PER_CTA, cnt);
+  rows_kernel<<<gr, NUSI_ROWS_PER_CTA * 6, 0, s>>>(G, d_params, c->d_rows, d_status);
   if (mid) CU(cudaEventRecord(mid, s));
   if (c->use_tiles) {
     dim3 gt(c->n_tiles, cnt);
@@ -371,21 +371,29 @@ static int launch_integrate(nusi_ctx *c, const PointParams *d_params, int cnt, d
                             cudaStream_t s) {
   const DeviceGrid &G = c->G;
   if (G.non_resonant) {
-    const int N = G.N;
-    int thr = 256;
-    if (N <= 256) thr = ((N + 31) / 32) * 32;
-    if (N <= thr)
-      integrate_kernel<1><<<cnt, thr, 0, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff);
-    else if (N <= 2 * 256)
-      integrate_kernel<2><<<cnt, 256, 0, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff);
-    else if (N <= 4 * 256)
-      integrate_kernel<4><<<cnt, 256, 0, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff);
-    else if (N <= 8 * 256)
-      integrate_kernel<8><<<cnt, 256, 0, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff);
-    else if (N <= 16 * 256)
-      integrate_kernel<16><<<cnt, 256, 0, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff);
-    else
-      return fail(NUSI_E_INVALID, "N_bins_E > 4096 is not supported by the integrator");
+    const int N = G.N, NT = G.NT, S = G.Nz - 1;
+    if (getenv("NUSI_SERIAL_INTEGRATOR")) {  // reference-shaped bin-by-bin kernel, kept for cross-checks
+      if (N > 256) return fail(NUSI_E_INVALID, "serial integrator supports N_bins_E <= 256");
+      integrate_kernel<1><<<cnt, ((N + 31) / 32) * 32, 0, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff);
+    } else {
+      const size_t sh = (size_t)(4 * NT + 2 * 32 + 2 * S) * sizeof(double);
+#define NUSI_WAVE(BPT, SB)                                                                                  \
+  do {                                                                                                      \
+    CU(cudaFuncSetAttribute(integrate_wave_kernel<BPT, SB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
+    integrate_wave_kernel<BPT, SB><<<cnt, 256, sh, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff); \
+  } while (0)
+      if (N <= 256 && NT <= 256 * 3)
+        NUSI_WAVE(1, 32);
+      else if (N <= 512 && NT <= 256 * 4)
+        NUSI_WAVE(2, 16);
+      else if (N <= 1024 && NT <= 256 * 6)
+        NUSI_WAVE(4, 8);
+      else if (N <= 2048 && NT <= 256 * 10)
+        NUSI_WAVE(8, 4);
+      else
+        return fail(NUSI_E_INVALID, "N_bins_E > 2048 is not supported by the integrator");
+#undef NUSI_WAVE
+    }
   } else {
     integrate_resonant_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(G, cnt, d_params, c->d_rows, c->d_tri, c->tstride,
                                                              c->d_work, d_fm, d_ff);

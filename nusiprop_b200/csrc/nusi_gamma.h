@@ -40,10 +40,12 @@ NUSI_HD double gamma_pp_closed(double a, double b) {
          2 * dilogdiff(4 / sqr(-2 + a + qa), 4 / sqr(-2 + b + qb));
 }
 
-// adds the contribution of target mass j to the running total `tot` of Gamma(Em, Ep), channel by
-// channel in the reference's order; *warn is set when the reference would print its
-// "Negative cross section when computing Gamma" message.
-NUSI_HD void gamma_mass(const PointParams &P, int j, double Em, double Ep, double &tot, int *warn) {
+// Channel contributions of target mass j to Gamma(Em, Ep), in the order the reference adds them
+// to its running total: ch[0..5] = s, t+u, tu, st, su, phiphi (each already weighted with
+// mphi^2/(2 m_j)); returns how many are filled (1 for resonant-only).  *warn is set when the
+// reference would print its "Negative cross section when computing Gamma" message.
+#define NUSI_GAMMA_NCH 6
+NUSI_HD int gamma_mass(const PointParams &P, int j, double Em, double Ep, double *ch, int *warn) {
   const double mphi = P.mphi, g = P.g, Ga = P.Ga;
   const double g4 = sqr(sqr(g));
   const double U2 = P.U2f[j];
@@ -67,8 +69,8 @@ NUSI_HD void gamma_mass(const PointParams &P, int j, double Em, double Ep, doubl
          (2 * mphi * atandiff(mphi * (splus - 1) / Ga, mphi * (sminus - 1) / Ga) + Ga * dlog);
   }
   Gs *= U2;
-  tot += wgt * Gs;
-  if (!P.non_resonant) return;
+  ch[0] = wgt * Gs;
+  if (!P.non_resonant) return 1;
 
   const double l1p = log1p(splus), l1m = log1p(sminus);
 
@@ -76,7 +78,7 @@ NUSI_HD void gamma_mass(const PointParams &P, int j, double Em, double Ep, doubl
   double Gtu_sum = g4 / (16 * kPi * sqr(mphi)) * (2 * l1p / splus - 2 * l1m / sminus + l1p - l1m);
   if (Gtu_sum < 0) Gtu_sum = g4 / (16 * kPi * sqr(mphi)) * gl3<gamma_tu_sum_integrand>(sminus, splus);
   Gtu_sum *= 2 * U2;  // same factor for Majorana and Dirac (nuSIprop.hpp:812-815)
-  tot += wgt * Gtu_sum;
+  ch[1] = wgt * Gtu_sum;
 
   /* t-u interference */
   double Gtu = g4 / (32 * kPi * sqr(mphi) * sminus * splus) *
@@ -85,7 +87,7 @@ NUSI_HD void gamma_mass(const PointParams &P, int j, double Em, double Ep, doubl
                 sminus * splus * (dilog1mdiff(splus, sminus) + dilogdiff(splus, sminus)));
   if (Gtu < 0) Gtu = g4 / (16 * kPi * sqr(mphi)) * gl3<gamma_tu_intf_integrand>(sminus, splus);
   Gtu *= P.majorana ? U2 : 0.5 * U2;
-  tot += wgt * Gtu;
+  ch[2] = wgt * Gtu;
 
   /* s-t interference */
   const double gr = Ga / mphi;
@@ -113,11 +115,11 @@ NUSI_HD void gamma_mass(const PointParams &P, int j, double Em, double Ep, doubl
                 2 * gr * carg_(1.0 - z2m) * l1m + log1p(4 / sqr(gr)) * (l1m - l1p) + lam_p * l1p -
                 lam_m * l1m + (1 + sqr(gr)) * (lam_m - lam_p) + 2 * dilogdiff(splus, sminus));
   Gst *= U2;
-  tot += wgt * Gst;
+  ch[3] = wgt * Gst;
 
   /* s-u interference: Majorana only */
   const double Gsu = P.majorana ? Gst : 0.0;
-  tot += wgt * Gsu;
+  ch[4] = wgt * Gsu;
 
   /* double-scalar production above threshold s = 4 mphi^2 */
   double Gpp = 0;
@@ -128,15 +130,20 @@ NUSI_HD void gamma_mass(const PointParams &P, int j, double Em, double Ep, doubl
     Gpp *= U2;
     if (P.majorana) Gpp *= 2;
   }
-  tot += wgt * Gpp;
+  ch[5] = wgt * Gpp;
 
   if (warn && (Gs < 0 || Gtu_sum < 0 || Gtu < 0 || (Gs + Gtu_sum + Gst + Gsu) < 0)) *warn |= 1;
+  return NUSI_GAMMA_NCH;
 }
 
 // Gamma(Em, Ep) = sum over the three target masses, accumulated in mass order like the reference
 NUSI_HD double gamma_row(const PointParams &P, double Em, double Ep, int *warn) {
   double tot = 0;
-  for (int j = 0; j < 3; ++j) gamma_mass(P, j, Em, Ep, tot, warn);
+  for (int j = 0; j < 3; ++j) {
+    double ch[NUSI_GAMMA_NCH];
+    const int n = gamma_mass(P, j, Em, Ep, ch, warn);
+    for (int c = 0; c < n; ++c) tot += ch[c];
+  }
   return tot;
 }
 

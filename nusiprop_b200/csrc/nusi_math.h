@@ -118,8 +118,9 @@ NUSI_HD double li2_core_real(double x) {
   return fma(w, fma(u, p, -0.25), u);
 }
 
-// Real part of Li2(x) for any real x (gsl_sf_dilog semantics).
-NUSI_HD double li2_real(double x) {
+// Real part of Li2(x) for any real x (gsl_sf_dilog semantics).  Not inlined: called from dozens of
+// sites, and the builder kernels must stay inside the instruction cache.
+NUSI_HD_NOINLINE double li2_real(double x) {
   if (x < -1.0) {
     const double l = log(-x);
     return -kZeta2 - 0.5 * l * l - li2_core_real(1.0 / x);
@@ -170,7 +171,7 @@ NUSI_HD cplx li2_unitdisk(double x, double y) {
 }
 
 // gsl_sf_complex_dilog_xy_e semantics.
-NUSI_HD cplx cli2(double x, double y) {
+NUSI_HD_NOINLINE cplx cli2(double x, double y) {
   if (y == 0.0) return mk(li2_real(x), (x >= 1.0) ? -kPi * log(x) : 0.0);
   const double r2 = x * x + y * y;
   if (r2 <= 1.0) return li2_unitdisk(x, y);
