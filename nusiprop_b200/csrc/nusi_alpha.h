@@ -21,25 +21,25 @@ namespace nusi {
 
 struct RowEdge {
   double t;      // t/mphi^2 at the edge, already moved off the pole t = -1 (nuSIprop.hpp:1257-1262)
-  double l1m;    // log1p(-t)
+  double l1m;    // nlog1p(-t)
   double labs;   // ln|1+t| as nuSIprop.hpp:1386-1387 computes it
-  double lfabs;  // log(fabs(1+t)) as the s-t interference writes it (nuSIprop.hpp:1456)
-  double lam2;   // log1p((2+t)^2/ga_red^2)
+  double lfabs;  // nlog(fabs(1+t)) as the s-t interference writes it (nuSIprop.hpp:1456)
+  double lam2;   // nlog1p((2+t)^2/ga_red^2)
   double argn;   // carg(-(1/(1+t))): pi if 1+t > 0 else 0
 };
 struct ColEdge {
   double s;      // s'/mphi^2 at the edge
-  double ls;     // log(s)
-  double lam;    // log1p((s-1)^2/ga_red^2)
+  double ls;     // nlog(s)
+  double lam;    // nlog1p((s-1)^2/ga_red^2)
   double args;   // carg(-1 + i ga_red + s)
-  double l2s;    // log((2+s)/s)
-  double ls2;    // log(s/(2+s))
+  double l2s;    // nlog((2+s)/s)
+  double ls2;    // nlog(s/(2+s))
 };
 struct Vertex {
-  double l1;     // log1p(s+t)
-  double lf;     // log(1+s+t)
+  double l1;     // nlog1p(s+t)
+  double lf;     // nlog(1+s+t)
   double dF;     // t < -1 ? Li2((1+s+t)/s) : Li2(s/(1+s+t))
-  double lq;     // log((1+s+t)/s)          (used only when t >= -1)
+  double lq;     // nlog((1+s+t)/s)          (used only when t >= -1)
   double d2;     // Li2((1+s+t)/(2+s))
   double zr_re, zr_im;  // gsl-style complex Li2 of the REAL number (1+s+t)/(1+t)
   double zc_re, zc_im;  // complex Li2 of (1+s+t)/(2 - i ga_red + t)
@@ -55,40 +55,40 @@ NUSI_HD double s_of(double mn, double E, double mphi) { return 2 * mn * E / sqr(
 
 NUSI_HD void make_row_edge(double t, double gr, bool full, RowEdge &R) {
   R.t = t;
-  R.l1m = log1p(-t);
+  R.l1m = nlog1p(-t);
   if (full) {
-    R.labs = (t > -1) ? log1p(t) : log(-1 - t);
-    R.lfabs = log(fabs(1 + t));
-    R.lam2 = log1p(sqr(2 + t) / sqr(gr));
+    R.labs = (t > -1) ? nlog1p(t) : nlog(-1 - t);
+    R.lfabs = nlog(fabs(1 + t));
+    R.lam2 = nlog1p(sqr(2 + t) / sqr(gr));
     R.argn = (-(1 / (1 + t)) < 0) ? kPi : 0.0;
   }
 }
 NUSI_HD void make_col_edge(double s, double gr, bool full, ColEdge &C) {
   C.s = s;
-  C.ls = log(s);
-  C.lam = log1p(sqr(-1 + s) / sqr(gr));
-  C.args = atan2(gr, -1 + s);
+  C.ls = nlog(s);
+  C.lam = nlog1p(sqr(-1 + s) / sqr(gr));
+  C.args = natan2(gr, -1 + s);
   if (full) {
-    C.l2s = log((2 + s) / s);
-    C.ls2 = log(s / (2 + s));
+    C.l2s = nlog((2 + s) / s);
+    C.ls2 = nlog(s / (2 + s));
   }
 }
 // everything of the Majorana closed forms that depends on one (s, t) pair
 NUSI_HD void make_vertex(double s, double t, double gr, Vertex &V) {
   const double one_st = 1 + s + t;
-  V.l1 = log1p(s + t);
-  V.lf = log(one_st);
+  V.l1 = nlog1p(s + t);
+  V.lf = nlog(one_st);
   if (t < -1) {
     V.dF = li2_real(one_st / s);
     V.lq = 0.0;
   } else {
     V.dF = li2_real(s / one_st);
-    V.lq = log(one_st / s);
+    V.lq = nlog(one_st / s);
   }
   V.d2 = li2_real(one_st / (2 + s));
   const double zr = one_st / (1 + t);
   V.zr_re = li2_real(zr);
-  V.zr_im = (zr >= 1.0) ? -kPi * log(zr) : 0.0;
+  V.zr_im = (zr >= 1.0) ? -kPi * nlog(zr) : 0.0;
   const cplx den = mk(2 + t, -gr);
   const cplx zc = one_st / den;
   const cplx dc = cli2(zc.re, zc.im);
@@ -133,11 +133,11 @@ NUSI_HD double alpha_s_colfactor(const PointParams &P, double sminus, double spl
 
 // double-scalar production, asymptotic forms above the tabulated range (nuSIprop.hpp:1487-1492)
 NUSI_HD double alpha_pp_asymptotic(double sm, double sp, double tm, double tp) {
-  const double lsm = log(sm), lsp = log(sp);
+  const double lsm = nlog(sm), lsp = nlog(sp);
   const double tail = (-6 * sm + 6 * sp - 2 * (-2 + sm) * sp * lsm + sm * sp * sqr(lsm) + 2 * sm * (-2 + sp) * lsp -
                        sm * sp * sqr(lsp));
   if (tm < -1) {
-    const double a = log(-1 - tm), b = log(-tm), c = log(-1 - tp), d = log(-tp);
+    const double a = nlog(-1 - tm), b = nlog(-tm), c = nlog(-1 - tp), d = nlog(-tp);
     return ((-sm + sp) * ((tm - tp) * (sp * (-2 + tm + tp) + sm * (-2 - 24 * sp + tm + tp)) +
                           4 * (-(sp * (1 + tm)) + sm * (-1 + 2 * sp + (-1 + sp) * tm)) * a +
                           2 * (3 * sp + sm * (3 + 4 * sp)) * tm * b +
@@ -149,7 +149,7 @@ NUSI_HD double alpha_pp_asymptotic(double sm, double sp, double tm, double tp) {
                 ((-3 - 2 * sm) * (tm - tp) + 2 * sqr(sm) * ((1 + tm) * a - tm * b - (1 + tp) * c + tp * d))) /
            (256. * kPi * sqr(sm) * sqr(sp));
   } else if (tp < -1) {
-    const double c = log(-1 - tp), d = log(-tp);
+    const double c = nlog(-1 - tp), d = nlog(-tp);
     return ((2 * sqr(sm) * lsp * ((1 + tp) * (-3 - 2 * sp + 2 * sqr(sp) * c) - 2 * sqr(sp) * tp * d) +
              (sm - sp) * ((1 + tp) * (-3 * (sm + sp + 8 * sm * sp) + (sm + sp) * tp) +
                           4 * (-(sp * (1 + tp)) + sm * (-1 + 2 * sp + (-1 + sp) * tp)) * c +
@@ -185,10 +185,10 @@ NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k
   const double gr = Ga / mphi;
   if (P.majorana) {
     /* t channel (u is identical for Majorana) */
-    const double LR1 = log(((1 + sm + tm) * (-1 + tp)) / ((-1 + tm) * (1 + sm + tp)));
-    const double LR2 = log(((1 + sp + tm) * (-1 + tp)) / ((-1 + tm) * (1 + sp + tp)));
-    const double LYm = log((sm * (1 + sp + tm)) / (sp * (1 + sm + tm)));
-    const double LYp = log((sm * (1 + sp + tp)) / (sp * (1 + sm + tp)));
+    const double LR1 = nlog(((1 + sm + tm) * (-1 + tp)) / ((-1 + tm) * (1 + sm + tp)));
+    const double LR2 = nlog(((1 + sp + tm) * (-1 + tp)) / ((-1 + tm) * (1 + sp + tp)));
+    const double LYm = nlog((sm * (1 + sp + tm)) / (sp * (1 + sm + tm)));
+    const double LYp = nlog((sm * (1 + sp + tp)) / (sp * (1 + sm + tp)));
     const double N1 = sm * sp * (-tm + tp) * Cm.ls + sm * sp * (tm - tp) * Cp.ls - sm * sp * Vmm.l1 -
                       sm * sp * tp * Vmm.l1 + sm * sp * Vpm.l1 + sm * sp * tp * Vpm.l1 - sp * LR1 - sp * tm * LR1 -
                       sp * tp * LR1 - sp * tm * tp * LR1 + sm * sp * Vmp.lf + sm * sp * tm * Vmp.l1 + sm * LR2 +
@@ -224,7 +224,7 @@ NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k
       F_tm = -Vmm.dF + Vpm.dF;
     else
       F_tm = Vmm.dF - Vpm.dF + 0.5 * (sqr(Vmm.lq) - sqr(Vpm.lq));
-    const double lmp = log(sm / sp);
+    const double lmp = nlog(sm / sp);
     a_tu = g4 / (32 * kPi * m4 * sm * sp * (1 + tm) * (1 + tp)) *
            (-4 * (sm - sp) * (1 + tm) * (tm - tp) * (1 + tp) + 2 * sm * sp * tp * (lmp - Vmm.l1 + Vpm.l1) +
             2 * sp * (1 + tm) * (1 + tp) * (Rm.l1m - Vmm.l1 - Rp.l1m + Vmp.l1) -
@@ -234,7 +234,7 @@ NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k
                 (Cm.l2s * (Cp.ls + Vmp.l1) - Cp.l2s * (Cm.ls + Vpp.l1) + Rp.l1m * (lmp - Vmp.l1 + Vpp.l1)) +
             sm * sp * (1 + tm) * (1 + tp) *
                 ((Cp.ls + Vmm.l1) * (Cm.ls2 + Rm.l1m - Rm.labs) + (Cm.ls + Vpm.l1) * (Cp.l2s - Rm.l1m + Rm.labs)) +
-            sm * sp * (log(sp / sm) + Vmp.l1 - Vpp.l1) * (2 * tm + (1 + tm) * (1 + tp) * Rp.labs) +
+            sm * sp * (nlog(sp / sm) + Vmp.l1 - Vpp.l1) * (2 * tm + (1 + tm) * (1 + tp) * Rp.labs) +
             sm * sp * (1 + tm) * (1 + tp) * (Vmm.d2 - Vpm.d2 - Vmp.d2 + Vpp.d2) +
             sm * sp * (1 + tm) * (1 + tp) * (F_tp + F_tm));
     // NB: the reference's quadrature fallback for a negative alpha_tu assigns to a shadowing local
@@ -273,7 +273,7 @@ NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k
   if ((sm > 4) && P.phiphi) {
     if (sm < 1e4) {
       const double delta = sp / sm;
-      a_pp = g4 / m4 * fabs(phiphi_alpha_eval(pp, sm, log(-sm / tm) / log(delta) * 1.0001, log10(delta), warn));
+      a_pp = g4 / m4 * fabs(phiphi_alpha_eval(pp, sm, nlog(-sm / tm) / nlog(delta) * 1.0001, log10(delta), warn));
     } else {
       a_pp = g4 / m4 * alpha_pp_asymptotic(sm, sp, tm, tp);
     }

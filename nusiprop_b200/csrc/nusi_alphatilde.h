@@ -43,18 +43,18 @@ NUSI_HD double atilde_t_core(double tminus, double tplus, double lm, double lp) 
 NUSI_HD double atilde_dilog_combi(double tminus, double tplus) {
   if (-tplus < 1e-2 && -tminus < 1e-2) {
     const double d = tplus / tminus;
-    return -(((-1 + d) * tplus * log(-2 * tplus)) / d) -
-           ((-1 + d) * sqr(tplus) * (-2 + d + d * log(2.) + log(-2 / tplus) - d * log(-tplus))) / (2. * sqr(d)) +
-           (cub(tplus) * (8 - 30 * d + 21 * sqr(d) + cub(d) - 8 * cub(d) * log(2.) + log(256.) + 8 * log(-tplus) -
-                          8 * cub(d) * log(-tplus))) /
+    return -(((-1 + d) * tplus * nlog(-2 * tplus)) / d) -
+           ((-1 + d) * sqr(tplus) * (-2 + d + d * nlog(2.) + nlog(-2 / tplus) - d * nlog(-tplus))) / (2. * sqr(d)) +
+           (cub(tplus) * (8 - 30 * d + 21 * sqr(d) + cub(d) - 8 * cub(d) * nlog(2.) + nlog(256.) + 8 * nlog(-tplus) -
+                          8 * cub(d) * nlog(-tplus))) /
                (24. * cub(d)) +
-           (sqr(sqr(tplus)) * (-32 + 56 * d - 51 * sqr(d) + 30 * cub(d) - 3 * sqr(sqr(d)) + log(4096.) -
-                               sqr(sqr(d)) * log(4096.) - 12 * log(-tplus) + 12 * sqr(sqr(d)) * log(-tplus))) /
+           (sqr(sqr(tplus)) * (-32 + 56 * d - 51 * sqr(d) + 30 * cub(d) - 3 * sqr(sqr(d)) + nlog(4096.) -
+                               sqr(sqr(d)) * nlog(4096.) - 12 * nlog(-tplus) + 12 * sqr(sqr(d)) * nlog(-tplus))) /
                (48. * sqr(sqr(d)));
   } else if (-tplus > 1e2 && -tminus > 1e2) {
     const double d = tplus / tminus;
-    const double lr = log((-1 + d) / d), lt = log(-tplus);
-    return (-2 * (-1 + d) * lr) / tplus - (2 * (-1 + log(-(d / ((-1 + d) * tplus))))) / sqr(tplus) +
+    const double lr = nlog((-1 + d) / d), lt = nlog(-tplus);
+    return (-2 * (-1 + d) * lr) / tplus - (2 * (-1 + nlog(-(d / ((-1 + d) * tplus))))) / sqr(tplus) +
            (-6 + 4 * d + sqr(d) - 2 * cub(d) - 8 * lr + 8 * d * lr + 2 * cub(d) * lr - 2 * sqr(sqr(d)) * lr - 6 * lt +
             6 * d * lt) /
                (3. * (-1 + d) * cub(tplus)) +
@@ -84,7 +84,7 @@ NUSI_HD int alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k,
 
   /* s channel */
   const double bw = sqr(mphi) / (sqr(mphi) + sqr(Ga));
-  const double dlog = log1p(bw * tplus * (tplus + 2)) - log1p(bw * tminus * (tminus + 2));
+  const double dlog = nlog1p(bw * tplus * (tplus + 2)) - nlog1p(bw * tminus * (tminus + 2));
   double As;
   if (fabs(tplus) < 1e-5) {
     const double gr = Ga / mphi;
@@ -102,9 +102,9 @@ NUSI_HD int alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k,
   ch[0] = wgt * As;
   if (!P.non_resonant) return 1;
 
-  const double lm = log1p(-tminus), lp = log1p(-tplus);  // ln(1-t-), ln(1-t+)
-  const double ld = log1p(tminus - tplus);               // ln(1 + t- - t+)
-  const double lrat = log(tminus / tplus);
+  const double lm = nlog1p(-tminus), lp = nlog1p(-tplus);  // ln(1-t-), ln(1-t+)
+  const double ld = nlog1p(tminus - tplus);               // ln(1 + t- - t+)
+  const double lrat = nlog(tminus / tplus);
 
   /* t channel, u channel */
   double At, Au;
@@ -178,9 +178,9 @@ NUSI_HD int alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k,
     dd26 = dilogdiff_complex(real_c(z2), real_c(z6));
     dd43 = dilogdiff_complex(z4, z3);
   }
-  const double arg_m = atan2(gr, -1 - tminus), arg_p = atan2(gr, -1 - tplus);  // carg(-1 + i ga_red - t)
+  const double arg_m = natan2(gr, -1 - tminus), arg_p = natan2(gr, -1 - tplus);  // carg(-1 + i ga_red - t)
   const double arg_qm = carg_(mk(gr, 1 + tminus) / den), arg_qp = carg_(mk(gr, 1 + tplus) / den);
-  const double lam_p = log1p(sqr(1 + tplus) / sqr(gr)), lam_m = log1p(sqr(1 + tminus) / sqr(gr));
+  const double lam_p = nlog1p(sqr(1 + tplus) / sqr(gr)), lam_m = nlog1p(sqr(1 + tminus) / sqr(gr));
   double Ast;
   if (P.majorana) {
     const double arg_1m = (1 + tminus < 0) ? kPi : 0.0;  // carg of the real number 1 + tminus
@@ -188,17 +188,17 @@ NUSI_HD int alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k,
           (2 * kPi * arg_m - 2 * kPi * arg_p + 2 * gr * (dd51.im + dd26.im + dd43.im) -
            2 * (dd51.re + dd26.re + dd43.re + dd78.re) - arg_qm * (2 * kPi + 2 * gr * lm) +
            arg_qp * (2 * kPi + 2 * gr * lp) + (arg_m - arg_p) * (4 * gr * tminus + 2 * gr * lm) +
-           2 * gr * (arg_1m - atan2(-gr, 2 + tminus) + atan2(-gr, 1 + tplus)) * ld +
-           log(4 + sqr(gr)) * (lp - lm) + log(sqr(gr) + sqr(2 + tminus)) * ld - 2 * lm * log(-tplus) -
-           2 * gr * kPi * (log(sqr(tplus)) + ld) + 2 * gr * kPi * log(sqr(tplus)) + 4 * tminus * lrat +
-           (-lp + lm - ld) * (lam_p + 2 * log(gr)) - ld * log1p(sqr(tminus) + 2 * tminus) +
-           2 * (sqr(gr) + tminus) * (lam_p - lam_m) + 2 * (log(-tplus) * (lp + ld) + (lam_p - lam_m)));
+           2 * gr * (arg_1m - natan2(-gr, 2 + tminus) + natan2(-gr, 1 + tplus)) * ld +
+           nlog(4 + sqr(gr)) * (lp - lm) + nlog(sqr(gr) + sqr(2 + tminus)) * ld - 2 * lm * nlog(-tplus) -
+           2 * gr * kPi * (nlog(sqr(tplus)) + ld) + 2 * gr * kPi * nlog(sqr(tplus)) + 4 * tminus * lrat +
+           (-lp + lm - ld) * (lam_p + 2 * nlog(gr)) - ld * nlog1p(sqr(tminus) + 2 * tminus) +
+           2 * (sqr(gr) + tminus) * (lam_p - lam_m) + 2 * (nlog(-tplus) * (lp + ld) + (lam_p - lam_m)));
   } else {
     const cplx s58 = dd51 + dd78;
     Ast = g4 / (32 * kPi * (1 + sqr(gr)) * m4) *
           (gr * dd51.im - 2 * (s58.re) + 2 * arg_qm * (-kPi - gr * lm) + 2 * arg_m * (kPi + gr * tminus + gr * lm) -
-           2 * arg_p * (kPi + gr * tminus + gr * lm) + 2 * arg_qp * (kPi + gr * lp) - 2 * lm * log(-tplus) +
-           2 * tminus * lrat + 2 * lp * log(-tplus) + (lp - lm) * (log(4 + sqr(gr)) - 2 * log(gr) - lam_p) +
+           2 * arg_p * (kPi + gr * tminus + gr * lm) + 2 * arg_qp * (kPi + gr * lp) - 2 * lm * nlog(-tplus) +
+           2 * tminus * lrat + 2 * lp * nlog(-tplus) + (lp - lm) * (nlog(4 + sqr(gr)) - 2 * nlog(gr) - lam_p) +
            (1 + tminus + sqr(gr)) * (lam_p - lam_m));
   }
   Ast *= U2;
@@ -215,10 +215,10 @@ NUSI_HD int alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k,
       App = g4 / m4 * phiphi_alphatilde_eval(pp, -tplus, log10(tplus / tminus), warn);
     } else {
       App = g4 / m4 *
-            (6 * tminus * log(-tminus) - tplus * sqr(log(-tminus)) +
-             2 * (-8 * tminus + 8 * tplus + 4 * tplus * log(-tminus) +
-                  log(tminus - tplus) * (tminus - tplus - tplus * lrat)) -
-             2 * (2 * tminus + 5 * tplus) * log(-tplus) + tplus * sqr(log(-tplus)) -
+            (6 * tminus * nlog(-tminus) - tplus * sqr(nlog(-tminus)) +
+             2 * (-8 * tminus + 8 * tplus + 4 * tplus * nlog(-tminus) +
+                  nlog(tminus - tplus) * (tminus - tplus - tplus * lrat)) -
+             2 * (2 * tminus + 5 * tplus) * nlog(-tplus) + tplus * sqr(nlog(-tplus)) -
              2 * tplus * li2_real(1 - tminus / tplus)) /
             (128. * kPi * tplus);
     }

@@ -35,7 +35,7 @@ NUSI_HD double atandiff(double x, double y) {
 
 // Li2(-x) - Li2(-y)  (aux.hpp:98-113)
 NUSI_HD double dilogdiff_large(double x) {
-  return -sqr(log(x)) / 2. + 1. / x - sqr(1. / x) / 4. + cub(1. / x) / 9. - sqr(sqr(1. / x)) / 16;
+  return -sqr(nlog(x)) / 2. + 1. / x - sqr(1. / x) / 4. + cub(1. / x) / 9. - sqr(sqr(1. / x)) / 16;
 }
 NUSI_HD double dilogdiff_small(double x) { return -x + sqr(x) / 4. - cub(x) / 9. + sqr(sqr(x)) / 16.; }
 NUSI_HD double dilogdiff(double x, double y) {
@@ -46,12 +46,12 @@ NUSI_HD double dilogdiff(double x, double y) {
 
 // Li2(-1-x) - Li2(-1-y)  (aux.hpp:115-130)
 NUSI_HD double dilog1m_large(double x) {
-  return -sqr(log(x)) / 2. + (1 - log(x)) / x + (-7 + 2 * log(x)) / (4. * sqr(x)) +
-         (19 - 3 * log(x)) / (9. * cub(x)) + (-125 + 12 * log(x)) / (48. * sqr(sqr(x)));
+  return -sqr(nlog(x)) / 2. + (1 - nlog(x)) / x + (-7 + 2 * nlog(x)) / (4. * sqr(x)) +
+         (19 - 3 * nlog(x)) / (9. * cub(x)) + (-125 + 12 * nlog(x)) / (48. * sqr(sqr(x)));
 }
 NUSI_HD double dilog1m_small(double x) {
-  return -x * log(2.) + (sqr(x) * (-1 + log(4.))) / 4. + (cub(x) * (5 - 8 * log(2.))) / 24. +
-         sqr(sqr(x)) * (-1. / 6. + log(2.) / 4.);
+  return -x * nlog(2.) + (sqr(x) * (-1 + nlog(4.))) / 4. + (cub(x) * (5 - 8 * nlog(2.))) / 24. +
+         sqr(sqr(x)) * (-1. / 6. + nlog(2.) / 4.);
 }
 NUSI_HD double dilog1mdiff(double x, double y) {
   if (x > 1e2 && y > 1e2) return dilog1m_large(x) - dilog1m_large(y);
@@ -61,12 +61,12 @@ NUSI_HD double dilog1mdiff(double x, double y) {
 
 // Li2(1+x) - Li2(1+y), x,y < 0  (aux.hpp:132-148)
 NUSI_HD double dilog1p_large(double x) {
-  return (-1 - 3 * log(-x)) / (9. * cub(x)) + (-1 - log(-x)) / x - sqr(log(-x)) / 2. +
-         (1 + 2 * log(-x)) / (4. * sqr(x)) + (1 + 4 * log(-x)) / (16. * sqr(sqr(x)));
+  return (-1 - 3 * nlog(-x)) / (9. * cub(x)) + (-1 - nlog(-x)) / x - sqr(nlog(-x)) / 2. +
+         (1 + 2 * nlog(-x)) / (4. * sqr(x)) + (1 + 4 * nlog(-x)) / (16. * sqr(sqr(x)));
 }
 NUSI_HD double dilog1p_small(double x) {
-  return x * (1 - log(-x)) + (sqr(x) * (-1 + 2 * log(-x))) / 4. + (cub(x) * (1 - 3 * log(-x))) / 9. +
-         (sqr(sqr(x)) * (-1 + 4 * log(-x))) / 16.;
+  return x * (1 - nlog(-x)) + (sqr(x) * (-1 + 2 * nlog(-x))) / 4. + (cub(x) * (1 - 3 * nlog(-x))) / 9. +
+         (sqr(sqr(x)) * (-1 + 4 * nlog(-x))) / 16.;
 }
 NUSI_HD double dilog1pdiff(double x, double y) {
   if (-x > 1e2 && -y > 1e2) return dilog1p_large(x) - dilog1p_large(y);
@@ -79,8 +79,8 @@ NUSI_HD double dilog1o1m_large(double x) {
   return -25 / (48. * sqr(sqr(x))) - 11 / (18. * cub(x)) - 3 / (4. * sqr(x)) - 1 / x;
 }
 NUSI_HD double dilog1o1m_small(double x) {
-  return (sqr(sqr(x)) * (-19 - 12 * log(-x))) / 48. + (cub(x) * (-7 - 6 * log(-x))) / 18. +
-         (sqr(x) * (-1 - 2 * log(-x))) / 4. + x * (1 - log(-x));
+  return (sqr(sqr(x)) * (-19 - 12 * nlog(-x))) / 48. + (cub(x) * (-7 - 6 * nlog(-x))) / 18. +
+         (sqr(x) * (-1 - 2 * nlog(-x))) / 4. + x * (1 - nlog(-x));
 }
 NUSI_HD double dilog1over1mdiff(double x, double y) {
   if (-x > 1e2 && -y > 1e2) return dilog1o1m_large(x) - dilog1o1m_large(y);

@@ -47,7 +47,9 @@ struct nusi_ctx {
   double *d_edgeE = nullptr;  // distinct bin-edge energies of the table cells (tiled builder)
   int2 *d_tiles = nullptr;
   int n_tiles = 0;
+  int n_edges = 0;
   bool use_tiles = false;
+  double *d_edges = nullptr;  // per-launch edge blocks [cap_points][edge_block_doubles]
   // per-launch work space (grown on demand)
   int cap_points = 0;
   size_t tstride = 0;
@@ -110,7 +112,7 @@ void nusi_ctx_destroy(nusi_ctx *c) {
   cudaSetDevice(c->opt.device);
   double *ptrs[] = {c->d_row_lo, c->d_row_hi, c->d_dE, c->d_cz, c->d_ndz, c->d_source, c->d_Emin, c->d_Emax,
                     c->d_zsrc, c->d_rsn, c->d_pp[0], c->d_pp[1], c->d_pp[2], c->d_pp[3], c->d_pp[4],
-                    c->d_rows, c->d_tri, c->d_work, c->d_edgeE};
+                    c->d_rows, c->d_tri, c->d_work, c->d_edgeE, c->d_edges};
   if (c->d_tiles) cudaFree(c->d_tiles);
   for (double *p : ptrs)
     if (p) cudaFree(p);
@@ -236,6 +238,7 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
         return fail(NUSI_E_CUDA, std::string("tile setup: ") + cudaGetErrorString(e1));
       }
       c->n_tiles = (int)tiles.size();
+      c->n_edges = (int)edge.size();
       c->use_tiles = true;
     }
   }
@@ -243,7 +246,7 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
   // chunk size: keep the packed tables of one launch within ~1/4 of free HBM, at most 8192 points
   size_t free_b = 0, total_b = 0;
   cudaMemGetInfo(&free_b, &total_b);
-  const size_t per_point = (c->tstride + 2 * (size_t)H.NT + 3 * (size_t)H.N) * sizeof(double);
+  const size_t per_point = (c->tstride + 2 * (size_t)H.NT + 3 * (size_t)H.N + edge_block_doubles(c->n_edges, H.NT)) * sizeof(double);
   size_t chunk = (free_b / 4) / per_point;
   if (chunk > 8192) chunk = 8192;
   if (chunk < 1) chunk = 1;
@@ -325,11 +328,13 @@ static int ensure_workspace(nusi_ctx *c, int npts) {
   if (c->d_rows) cudaFree(c->d_rows);
   if (c->d_tri) cudaFree(c->d_tri);
   if (c->d_work) cudaFree(c->d_work);
-  c->d_rows = c->d_tri = c->d_work = nullptr;
+  if (c->d_edges) cudaFree(c->d_edges);
+  c->d_rows = c->d_tri = c->d_work = c->d_edges = nullptr;
   c->cap_points = 0;
   CU(cudaMalloc((void **)&c->d_rows, (size_t)npts * 2 * c->H.NT * sizeof(double)));
   CU(cudaMalloc((void **)&c->d_tri, (size_t)npts * c->tstride * sizeof(double)));
   if (!c->G.non_resonant) CU(cudaMalloc((void **)&c->d_work, (size_t)npts * 3 * c->H.N * sizeof(double)));
+  if (c->use_tiles) CU(cudaMalloc((void **)&c->d_edges, (size_t)npts * edge_block_doubles(c->n_edges, c->H.NT) * sizeof(double)));
   c->cap_points = npts;
   return NUSI_OK;
 }
@@ -355,8 +360,13 @@ static int launch_xsec(nusi_ctx *c, const PointParams *d_params, int cnt, int *d
   rows_kernel<<<gr, NUSI_ROWS_PER_CTA * 6, 0, s>>>(G, d_params, c->d_rows, d_status);
   if (mid) CU(cudaEventRecord(mid, s));
   if (c->use_tiles) {
+    const int ntask = 3 * (2 * c->n_edges + G.NT);
+    dim3 ge((ntask + 127) / 128, cnt);
+    edges_kernel<<<ge, 128, 0, s>>>(G, c->n_edges, d_params, c->d_edgeE, c->d_edges);
     dim3 gt(c->n_tiles, cnt);
-    alpha_tile_kernel<<<gt, 256, sizeof(TileSmem), s>>>(G, d_params, c->d_edgeE, c->d_tiles, c->d_tri, c->tstride, d_status);
+    alpha_tile_kernel<<<gt, 256, sizeof(TileSmem), s>>>(G, c->n_edges, d_params, c->d_edgeE, c->d_edges, c->d_tiles, c->d_tri,
+                                                       c->tstride, d_status);
+    c->n_launches += 1;
   } else {
     const long long nent = G.non_resonant ? (long long)G.NT * (G.NT - 1) / 2 : (long long)(G.NT - 1);
     dim3 ga((unsigned)((nent + 127) / 128), cnt);

@@ -10,13 +10,13 @@
 namespace nusi {
 
 // integrands of the three fallbacks (nuSIprop.hpp:809, 833, 900)
-NUSI_HD double gamma_tu_sum_integrand(double z) { return (z + 2) / (z * (z + 1)) - 2 / sqr(z) * log1p(z); }
+NUSI_HD double gamma_tu_sum_integrand(double z) { return (z + 2) / (z * (z + 1)) - 2 / sqr(z) * nlog1p(z); }
 NUSI_HD double gamma_tu_intf_integrand(double z) {
-  return 1 / z - 2 * (1 + z) / (sqr(z) * (2 + z)) * log1p(z);
+  return 1 / z - 2 * (1 + z) / (sqr(z) * (2 + z)) * nlog1p(z);
 }
 NUSI_HD double gamma_pp_integrand(double z) {
   const double q = sqrt(z * (z - 4));
-  return (sqr(z) - 4 * z + 6) / (sqr(z) * (z - 2)) * log(sqr((q + z - 2) / (q - z + 2))) - 6 * q / sqr(z);
+  return (sqr(z) - 4 * z + 6) / (sqr(z) * (z - 2)) * nlog(sqr((q + z - 2) / (q - z + 2))) - 6 * q / sqr(z);
 }
 template <double (*F)(double)>
 NUSI_HD double gl3(double a, double b) {
@@ -31,11 +31,11 @@ NUSI_HD double gamma_pp_closed(double a, double b) {
   const double qa = sqrt((-4 + a) * a), qb = sqrt((-4 + b) * b);
   const double ra = sqrt((-4 + a) / a), rb = sqrt((-4 + b) / b);
   const double sa = sqrt(-4 + a), sb = sqrt(-4 + b), wa = sqrt(a), wb = sqrt(b);
-  return 12 * ra - 12 * rb - 2 * log(sqr(sa - wa) / 4.) * log(sqr(-2 + a + qa) / 4.) -
-         ((6 + a * log((-2 + a) * a)) * log(sqr(-2 + a + qa) / sqr(2 - a + qa))) / a -
-         24 * (ra - rb - log(sa + wa) + log(sb + wb)) +
-         2 * log(sqr(sb - wb) / 4.) * log(sqr(-2 + b + qb) / 4.) +
-         ((6 + b * log((-2 + b) * b)) * log(sqr(-2 + b + qb) / sqr(2 - b + qb))) / b +
+  return 12 * ra - 12 * rb - 2 * nlog(sqr(sa - wa) / 4.) * nlog(sqr(-2 + a + qa) / 4.) -
+         ((6 + a * nlog((-2 + a) * a)) * nlog(sqr(-2 + a + qa) / sqr(2 - a + qa))) / a -
+         24 * (ra - rb - nlog(sa + wa) + nlog(sb + wb)) +
+         2 * nlog(sqr(sb - wb) / 4.) * nlog(sqr(-2 + b + qb) / 4.) +
+         ((6 + b * nlog((-2 + b) * b)) * nlog(sqr(-2 + b + qb) / sqr(2 - b + qb))) / b +
          8 * dilogdiff(4 / sqr(sa + wa), 4 / sqr(sb + wb)) +
          2 * dilogdiff(4 / sqr(-2 + a + qa), 4 / sqr(-2 + b + qb));
 }
@@ -55,7 +55,7 @@ NUSI_HD int gamma_mass(const PointParams &P, int j, double Em, double Ep, double
 
   /* s channel: Breit-Wigner integrated over the bin */
   const double bw = sqr(mphi) / (sqr(mphi) + sqr(Ga));
-  const double dlog = log1p(bw * splus * (splus - 2)) - log1p(bw * sminus * (sminus - 2));
+  const double dlog = nlog1p(bw * splus * (splus - 2)) - nlog1p(bw * sminus * (sminus - 2));
   double Gs;
   if (splus < 1e-5) {
     const double gr = Ga / mphi;
@@ -72,7 +72,7 @@ NUSI_HD int gamma_mass(const PointParams &P, int j, double Em, double Ep, double
   ch[0] = wgt * Gs;
   if (!P.non_resonant) return 1;
 
-  const double l1p = log1p(splus), l1m = log1p(sminus);
+  const double l1p = nlog1p(splus), l1m = nlog1p(sminus);
 
   /* t + u without interference */
   double Gtu_sum = g4 / (16 * kPi * sqr(mphi)) * (2 * l1p / splus - 2 * l1m / sminus + l1p - l1m);
@@ -82,8 +82,8 @@ NUSI_HD int gamma_mass(const PointParams &P, int j, double Em, double Ep, double
 
   /* t-u interference */
   double Gtu = g4 / (32 * kPi * sqr(mphi) * sminus * splus) *
-               (sminus * l1p * (2 + 2 * splus + splus * log(2 + splus)) -
-                splus * l1m * (2 + 2 * sminus + sminus * log(2 + sminus)) +
+               (sminus * l1p * (2 + 2 * splus + splus * nlog(2 + splus)) -
+                splus * l1m * (2 + 2 * sminus + sminus * nlog(2 + sminus)) +
                 sminus * splus * (dilog1mdiff(splus, sminus) + dilogdiff(splus, sminus)));
   if (Gtu < 0) Gtu = g4 / (16 * kPi * sqr(mphi)) * gl3<gamma_tu_intf_integrand>(sminus, splus);
   Gtu *= P.majorana ? U2 : 0.5 * U2;
@@ -109,10 +109,10 @@ NUSI_HD int gamma_mass(const PointParams &P, int j, double Em, double Ep, double
     dd1 = dilogdiff_complex(z1p, z1m);
     dd2 = dilogdiff_complex(z2p, z2m);
   }
-  const double lam_p = log1p(sqr(-1 + splus) / sqr(gr)), lam_m = log1p(sqr(-1 + sminus) / sqr(gr));
+  const double lam_p = nlog1p(sqr(-1 + splus) / sqr(gr)), lam_m = nlog1p(sqr(-1 + sminus) / sqr(gr));
   double Gst = -g4 / (32 * kPi * sqr(mphi) * (1 + sqr(gr))) *
                (dd1.re + dd2.re + gr * (dd2.im - dd1.im) + 2 * gr * carg_(1.0 - z2p) * l1p -
-                2 * gr * carg_(1.0 - z2m) * l1m + log1p(4 / sqr(gr)) * (l1m - l1p) + lam_p * l1p -
+                2 * gr * carg_(1.0 - z2m) * l1m + nlog1p(4 / sqr(gr)) * (l1m - l1p) + lam_p * l1p -
                 lam_m * l1m + (1 + sqr(gr)) * (lam_m - lam_p) + 2 * dilogdiff(splus, sminus));
   Gst *= U2;
   ch[3] = wgt * Gst;

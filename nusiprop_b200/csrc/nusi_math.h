@@ -35,6 +35,19 @@
 
 namespace nusi {
 
+// Elementary functions.  On the device each is ONE out-of-line copy (CUDA inlines ~1-3 KB of SASS
+// per call site otherwise, and the builder kernels have ~60 call sites: the instruction cache is
+// the first bottleneck of this path).  On the host they are the libm calls.
+#if defined(__CUDA_ARCH__)
+__device__ __noinline__ double nlog(double x) { return ::log(x); }
+__device__ __noinline__ double nlog1p(double x) { return ::log1p(x); }
+__device__ __noinline__ double natan2(double y, double x) { return ::atan2(y, x); }
+#else
+inline double nlog(double x) { return ::log(x); }
+inline double nlog1p(double x) { return ::log1p(x); }
+inline double natan2(double y, double x) { return ::atan2(y, x); }
+#endif
+
 static const double kPi = 3.14159265358979323846264338328;
 static const double kZeta2 = 1.6449340668482264364724151666460;  // pi^2/6
 
@@ -77,8 +90,8 @@ NUSI_HD cplx operator/(cplx a, cplx b) {
 NUSI_HD cplx operator/(double s, cplx b) { return mk(s, 0.0) / b; }
 NUSI_HD cplx conj(cplx a) { return mk(a.re, -a.im); }
 NUSI_HD double cabs_(cplx a) { return hypot(a.re, a.im); }
-NUSI_HD double carg_(cplx a) { return atan2(a.im, a.re); }
-NUSI_HD cplx clog_(cplx a) { return mk(log(hypot(a.re, a.im)), atan2(a.im, a.re)); }
+NUSI_HD double carg_(cplx a) { return natan2(a.im, a.re); }
+NUSI_HD cplx clog_(cplx a) { return mk(nlog(hypot(a.re, a.im)), natan2(a.im, a.re)); }
 NUSI_HD cplx csqr(cplx a) { return a * a; }
 NUSI_HD cplx ccub(cplx a) { return a * a * a; }
 
@@ -100,10 +113,8 @@ NUSI_HD cplx ccub(cplx a) { return a * a * a; }
 #define NUSI_BERN_12 -5.5817858743250093e-21
 #define NUSI_BERN_13 1.3091507554183213e-22
 
-// Li2 for real x in [-1, 1/2]:  u = -log1p(-x) in [-0.6932, 0.6932]; (u/2pi)^2 <= 0.0122
-// so 9 Bernoulli terms leave a tail < 1e-19 relative.
-NUSI_HD double li2_core_real(double x) {
-  const double u = -log1p(-x);
+// Li2(y) from u = -ln(1-y), |u| <= 0.6932: (u/2pi)^2 <= 0.0122, 9 Bernoulli terms leave < 1e-19.
+NUSI_HD double li2_from_u(double u) {
   const double w = u * u;
   double p = NUSI_BERN_9;
   p = fma(p, w, NUSI_BERN_8);
@@ -114,73 +125,102 @@ NUSI_HD double li2_core_real(double x) {
   p = fma(p, w, NUSI_BERN_3);
   p = fma(p, w, NUSI_BERN_2);
   p = fma(p, w, NUSI_BERN_1);
-  // u - u^2/4 + u^3 p
-  return fma(w, fma(u, p, -0.25), u);
+  return fma(w, fma(u, p, -0.25), u);  // u - u^2/4 + u^3 p
 }
 
-// Real part of Li2(x) for any real x (gsl_sf_dilog semantics).  Not inlined: called from dozens of
-// sites, and the builder kernels must stay inside the instruction cache.
+// Real part of Li2(x) for any real x (gsl_sf_dilog semantics).  Every branch reduces to ONE core
+// evaluation; where the reduced argument is 1-x the core's u = -ln(x) is the logarithm the
+// reflection term needs anyway, so it is computed once.
 NUSI_HD_NOINLINE double li2_real(double x) {
-  if (x < -1.0) {
-    const double l = log(-x);
-    return -kZeta2 - 0.5 * l * l - li2_core_real(1.0 / x);
+  double u, add, sign;
+  if (x < -1.0) {  // inversion: -zeta2 - ln^2(-x)/2 - Li2(1/x)
+    const double l = nlog(-x);
+    u = -nlog1p(-1.0 / x);
+    add = -kZeta2 - 0.5 * l * l;
+    sign = -1.0;
   } else if (x <= 0.5) {
-    return li2_core_real(x);
-  } else if (x < 1.0) {
-    return kZeta2 - log(x) * log1p(-x) - li2_core_real(1.0 - x);
+    u = -nlog1p(-x);
+    add = 0.0;
+    sign = 1.0;
+  } else if (x < 1.0) {  // reflection: zeta2 - ln(x) ln(1-x) - Li2(1-x)
+    const double lx = nlog(x);
+    u = -lx;
+    add = kZeta2 - lx * nlog1p(-x);
+    sign = -1.0;
   } else if (x == 1.0) {
     return kZeta2;
-  } else if (x <= 2.0) {
-    return kZeta2 - log(x) * log(x - 1.0) - li2_core_real(1.0 - x);
-  } else {
-    const double l = log(x);
-    return 2.0 * kZeta2 - 0.5 * l * l - li2_core_real(1.0 / x);
+  } else if (x <= 2.0) {  // zeta2 - ln(x) ln(x-1) - Li2(1-x)
+    const double lx = nlog(x);
+    u = -lx;
+    add = kZeta2 - lx * nlog(x - 1.0);
+    sign = -1.0;
+  } else {  // pi^2/3 - ln^2(x)/2 - Li2(1/x)
+    const double l = nlog(x);
+    u = -nlog1p(-1.0 / x);
+    add = 2.0 * kZeta2 - 0.5 * l * l;
+    sign = -1.0;
   }
+  return add + sign * li2_from_u(u);
 }
 
-// Complex core: |w| <= 1 and Re w <= 1/2  =>  |u| <= 1.256, (|u|/2pi)^2 <= 0.04: 13 terms.
-NUSI_HD cplx li2_core_cplx(double x, double y) {
-  const cplx u = mk(-0.5 * log1p((x * x - 2.0 * x) + y * y), -atan2(-y, 1.0 - x));
-  const cplx w = u * u;
-  cplx p = mk(NUSI_BERN_13, 0.0);
-  p = p * w + NUSI_BERN_12;
-  p = p * w + NUSI_BERN_11;
-  p = p * w + NUSI_BERN_10;
-  p = p * w + NUSI_BERN_9;
-  p = p * w + NUSI_BERN_8;
-  p = p * w + NUSI_BERN_7;
-  p = p * w + NUSI_BERN_6;
-  p = p * w + NUSI_BERN_5;
-  p = p * w + NUSI_BERN_4;
-  p = p * w + NUSI_BERN_3;
-  p = p * w + NUSI_BERN_2;
-  p = p * w + NUSI_BERN_1;
-  return u + w * ((u * p) - 0.25);
-}
-
-// Li2 on the closed unit disk (y != 0 handled by caller for the real axis).
-NUSI_HD cplx li2_unitdisk(double x, double y) {
-  if (x > 0.5) {
-    // reflection  Li2(w) = -Li2(1-w) + zeta2 - ln(w) ln(1-w)
-    const cplx t = li2_core_cplx(1.0 - x, -y);
-    const double lnz = 0.5 * log(x * x + y * y), argz = atan2(y, x);
-    const double lnomz = 0.5 * log((1.0 - x) * (1.0 - x) + y * y), argomz = atan2(-y, 1.0 - x);
-    return mk(-t.re + kZeta2 - lnz * lnomz + argz * argomz, -t.im - argz * lnomz - argomz * lnz);
+// Complex core from u = -ln(1-w): |w| <= 1 and Re w <= 1/2  =>  |u| <= 1.256, (|u|/2pi)^2 <= 0.04.
+NUSI_HD cplx li2_from_u_cplx(cplx u) {
+  const double wr = u.re * u.re - u.im * u.im, wi = 2.0 * (u.re * u.im);
+  double pr = NUSI_BERN_13, pi = 0.0;
+#define NUSI_CSTEP(C)                          \
+  {                                            \
+    const double tr = fma(pr, wr, fma(-pi, wi, C)); \
+    pi = fma(pr, wi, pi * wr);                 \
+    pr = tr;                                   \
   }
-  return li2_core_cplx(x, y);
+  NUSI_CSTEP(NUSI_BERN_12)
+  NUSI_CSTEP(NUSI_BERN_11)
+  NUSI_CSTEP(NUSI_BERN_10)
+  NUSI_CSTEP(NUSI_BERN_9)
+  NUSI_CSTEP(NUSI_BERN_8)
+  NUSI_CSTEP(NUSI_BERN_7)
+  NUSI_CSTEP(NUSI_BERN_6)
+  NUSI_CSTEP(NUSI_BERN_5)
+  NUSI_CSTEP(NUSI_BERN_4)
+  NUSI_CSTEP(NUSI_BERN_3)
+  NUSI_CSTEP(NUSI_BERN_2)
+  NUSI_CSTEP(NUSI_BERN_1)
+#undef NUSI_CSTEP
+  // u + w (u p - 1/4)
+  const double qr = fma(u.re, pr, fma(-u.im, pi, -0.25)), qi = fma(u.re, pi, u.im * pr);
+  return mk(fma(wr, qr, fma(-wi, qi, u.re)), fma(wr, qi, fma(wi, qr, u.im)));
 }
 
-// gsl_sf_complex_dilog_xy_e semantics.
+// gsl_sf_complex_dilog_xy_e semantics: y == 0.0 exactly -> (Re Li2(x), x >= 1 ? -pi ln x : 0);
+// |z| > 1 -> inversion Li2(z) = -Li2(1/z) - zeta2 - ln^2(-z)/2 with Im ln(-z) = sgn(th)(|th|-pi);
+// Re w > 1/2 -> reflection Li2(w) = -Li2(1-w) + zeta2 - ln(w) ln(1-w).  One core evaluation.
 NUSI_HD_NOINLINE cplx cli2(double x, double y) {
-  if (y == 0.0) return mk(li2_real(x), (x >= 1.0) ? -kPi * log(x) : 0.0);
+  if (y == 0.0) return mk(li2_real(x), (x >= 1.0) ? -kPi * nlog(x) : 0.0);
   const double r2 = x * x + y * y;
-  if (r2 <= 1.0) return li2_unitdisk(x, y);
-  // inversion  Li2(z) = -Li2(1/z) - zeta2 - ln^2(-z)/2,  Im ln(-z) = sgn(theta)(|theta|-pi)
-  const cplx t = li2_unitdisk(x / r2, -y / r2);
-  const double th = atan2(y, x);
-  const double lre = 0.5 * log(r2);
-  const double lim = (th < 0.0 ? -1.0 : 1.0) * (fabs(th) - kPi);
-  return mk(-t.re - 0.5 * (lre * lre - lim * lim) - kZeta2, -t.im - lre * lim);
+  const bool inv = r2 > 1.0;
+  double wx = x, wy = y;
+  if (inv) {
+    wx = x / r2;
+    wy = -y / r2;
+  }
+  const bool refl = wx > 0.5;
+  // ln(1-w) = (lnomw, argomw) and, if reflected, ln(w) = (lnw, argw)
+  const double lnomw = 0.5 * nlog1p((wx * wx - 2.0 * wx) + wy * wy), argomw = natan2(-wy, 1.0 - wx);
+  cplx res;
+  if (refl) {
+    const double lnw = 0.5 * nlog(wx * wx + wy * wy), argw = natan2(wy, wx);
+    const cplx t = li2_from_u_cplx(mk(-lnw, -argw));  // Li2(1-w): u = -ln(w)
+    res = mk(-t.re + kZeta2 - lnw * lnomw + argw * argomw, -t.im - argw * lnomw - argomw * lnw);
+  } else {
+    res = li2_from_u_cplx(mk(-lnomw, -argomw));
+  }
+  if (inv) {
+    const double th = natan2(y, x);
+    const double lre = 0.5 * nlog(r2);
+    const double lim = (th < 0.0 ? -1.0 : 1.0) * (fabs(th) - kPi);
+    res = mk(-res.re - 0.5 * (lre * lre - lim * lim) - kZeta2, -res.im - lre * lim);
+  }
+  return res;
 }
 
 // ----------------------------------------------------------------------------------------
