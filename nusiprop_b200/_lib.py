@@ -26,6 +26,7 @@ class NusiOpts(C.Structure):
         ("alpha_phiphi_path", C.c_char_p),
         ("device", C.c_int),
         ("max_points_per_launch", C.c_int),
+        ("elementary_mode", C.c_int),
     ]
 
 

@@ -31,7 +31,7 @@ class Context(object):
 
     def __init__(self, majorana=True, non_resonant=True, normal_ordering=True, N_bins_E=300, lEmin=12.0,
                  lEmax=17.0, zmax=5.0, flav=2, phiphi=False, device=0, alphatilde_phiphi_path=None,
-                 alpha_phiphi_path=None, max_points_per_launch=0):
+                 alpha_phiphi_path=None, max_points_per_launch=0, elementary_mode=None):
         self._lib = _lib.load()
         o = NusiOpts()
         check(self._lib.nusi_opts_default(C.byref(o)), "nusi_opts_default")
@@ -39,6 +39,8 @@ class Context(object):
         o.N_bins_E, o.lEmin, o.lEmax, o.zmax, o.flav, o.phiphi = int(N_bins_E), float(lEmin), float(lEmax), float(zmax), int(flav), int(bool(phiphi))
         o.device = int(device)
         o.max_points_per_launch = int(max_points_per_launch)
+        if elementary_mode is not None:
+            o.elementary_mode = int(elementary_mode)
         self._paths = (
             alphatilde_phiphi_path.encode() if alphatilde_phiphi_path else None,
             alpha_phiphi_path.encode() if alpha_phiphi_path else None,

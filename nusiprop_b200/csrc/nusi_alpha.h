@@ -26,6 +26,8 @@ struct RowEdge {
   double lfabs;  // nlog(fabs(1+t)) as the s-t interference writes it (nuSIprop.hpp:1456)
   double lam2;   // nlog1p((2+t)^2/ga_red^2)
   double argn;   // carg(-(1/(1+t))): pi if 1+t > 0 else 0
+  double lnD;    // ln((2+t)^2 + ga_red^2) = lam2 + 2 ln(ga_red)        (shared-logarithm builder)
+  double phi;    // arg(2 + t + i ga_red) in (0, pi)                     (shared-logarithm builder)
 };
 struct ColEdge {
   double s;      // s'/mphi^2 at the edge
@@ -34,6 +36,8 @@ struct ColEdge {
   double args;   // carg(-1 + i ga_red + s)
   double l2s;    // nlog((2+s)/s)
   double ls2;    // nlog(s/(2+s))
+  double l2;     // ln(2+s)                                               (shared-logarithm builder)
+  double lnN;    // ln((s-1)^2 + ga_red^2) = lam + 2 ln(ga_red)           (shared-logarithm builder)
 };
 struct Vertex {
   double l1;     // nlog1p(s+t)
@@ -61,6 +65,8 @@ NUSI_HD void make_row_edge(double t, double gr, bool full, RowEdge &R) {
     R.lfabs = nlog(fabs(1 + t));
     R.lam2 = nlog1p(sqr(2 + t) / sqr(gr));
     R.argn = (-(1 / (1 + t)) < 0) ? kPi : 0.0;
+    R.lnD = R.lam2 + 2 * nlog(gr);
+    R.phi = natan2(gr, 2 + t);
   }
 }
 NUSI_HD void make_col_edge(double s, double gr, bool full, ColEdge &C) {
@@ -71,6 +77,8 @@ NUSI_HD void make_col_edge(double s, double gr, bool full, ColEdge &C) {
   if (full) {
     C.l2s = nlog((2 + s) / s);
     C.ls2 = nlog(s / (2 + s));
+    C.l2 = nlog(2 + s);
+    C.lnN = C.lam + 2 * nlog(gr);
   }
 }
 // everything of the Majorana closed forms that depends on one (s, t) pair
@@ -95,6 +103,77 @@ NUSI_HD void make_vertex(double s, double t, double gr, Vertex &V) {
   V.zc_re = dc.re;
   V.zc_im = dc.im;
   V.ca = carg_(-(mk(-1 + s, gr) / den));
+}
+
+// ---- shared-logarithm vertex ------------------------------------------------------------
+// Every logarithm and argument that make_vertex() evaluates is, in exact arithmetic, a signed sum
+// of ONE vertex logarithm  l1 = ln(1+s+t)  and logarithms / arguments of the two edges:
+//   ln(s/(1+s+t)) = ls - l1            ln((1+t)/(1+s+t)) = labs - l1      (dF, t > -1)
+//   ln((1+s+t)/(2+s)) = l1 - l2        ln((1-t)/(2+s))   = l1m - l2       (d2)
+//   ln zr = l1 - labs,  ln(zr-1) = ls - labs,  ln(1-zr) = ls - labs        (zr = (1+s+t)/(1+t))
+//   ln|zc| = l1 - lnD/2,  arg zc = phi,  ln|1-zc| = (lnN - lnD)/2,  arg(1-zc) = args - pi + phi
+//   arg(-(s-1+i ga)/(2+t-i ga)) = args + phi - pi
+// so a vertex costs one log1p plus the polynomial cores; the floating-point result differs from
+// make_vertex() by a few ulp of the logarithms involved (the size of the glibc-vs-CUDA libm
+// difference), which is why both builders exist: opts.strict selects make_vertex().
+NUSI_HD double li2_unit_logs(double x, double lnx, double ln1mx) {  // Li2(x), 0 < x < 1
+  return (x <= 0.5) ? li2_from_u(-ln1mx) : kZeta2 - lnx * ln1mx - li2_from_u(-lnx);
+}
+NUSI_HD void make_vertex_shared(const RowEdge &R, const ColEdge &C, double gr, Vertex &V) {
+  const double s = C.s, t = R.t;
+  const double one_st = 1 + s + t;
+  const double l1 = nlog1p(s + t);
+  V.l1 = l1;
+  V.lf = l1;
+  // FCTR dilogarithm (nuSIprop.hpp:1373-1384)
+  if (t < -1) {
+    V.dF = li2_unit_logs(one_st / s, l1 - C.ls, R.labs - C.ls);
+    V.lq = 0.0;
+  } else {
+    V.dF = li2_unit_logs(s / one_st, C.ls - l1, R.labs - l1);
+    V.lq = l1 - C.ls;
+  }
+  V.d2 = li2_unit_logs(one_st / (2 + s), l1 - C.l2, R.l1m - C.l2);
+  // real-axis dilogarithm of zr = (1+s+t)/(1+t) with GSL's imaginary part
+  const double zr = one_st / (1 + t);
+  const double lnzr = l1 - R.labs;  // ln|zr|
+  if (zr > 2.0) {
+    V.zr_re = 2.0 * kZeta2 - 0.5 * lnzr * lnzr - li2_from_u(l1 - C.ls);
+  } else if (zr > 1.0) {
+    V.zr_re = kZeta2 - lnzr * (C.ls - R.labs) - li2_from_u(-lnzr);
+  } else if (zr == 1.0) {
+    V.zr_re = kZeta2;
+  } else if (zr < -1.0) {
+    V.zr_re = -kZeta2 - 0.5 * lnzr * lnzr - li2_from_u(l1 - C.ls);
+  } else {  // -1 <= zr < 0 (zr in [0,1) cannot occur: s > 0)
+    V.zr_re = li2_from_u(R.labs - C.ls);
+  }
+  V.zr_im = (zr >= 1.0) ? -kPi * lnzr : 0.0;
+  // complex dilogarithm of zc = (1+s+t)/(2 - i ga + t), same case split as cli2()
+  const double D = sqr(2 + t) + sqr(gr);
+  const double x = one_st * (2 + t) / D, y = one_st * gr / D;
+  const double r2 = x * x + y * y;
+  const bool inv = r2 > 1.0;
+  const double wx = inv ? x / r2 : x;
+  const bool refl = wx > 0.5;
+  const double lnr = l1 - 0.5 * R.lnD;  // ln|zc|
+  const double lnw = inv ? -lnr : lnr, argw = inv ? -R.phi : R.phi;
+  const double lnomw = inv ? 0.5 * C.lnN - l1 : 0.5 * (C.lnN - R.lnD);
+  const double argomw = inv ? C.args : C.args - kPi + R.phi;
+  cplx res;
+  if (refl) {
+    const cplx tt = li2_from_u_cplx(mk(-lnw, -argw));
+    res = mk(-tt.re + kZeta2 - lnw * lnomw + argw * argomw, -tt.im - argw * lnomw - argomw * lnw);
+  } else {
+    res = li2_from_u_cplx(mk(-lnomw, -argomw));
+  }
+  if (inv) {
+    const double lim = R.phi - kPi;  // theta = phi > 0
+    res = mk(-res.re - 0.5 * (lnr * lnr - lim * lim) - kZeta2, -res.im - lnr * lim);
+  }
+  V.zc_re = res.re;
+  V.zc_im = res.im;
+  V.ca = C.args + R.phi - kPi;
 }
 
 // 3x3 Gauss-Legendre fallback on  y in [t+, t-], x in [s-, s+]  (nuSIprop.hpp:1288-1303 etc.)
@@ -165,7 +244,12 @@ NUSI_HD double alpha_pp_asymptotic(double sm, double sp, double tm, double tp) {
 //   Rm,Rp  row edges t-, t+      Cm,Cp  column edges s'-, s'+
 //   Vmm = (s-,t-)  Vpm = (s+,t-)  Vmp = (s-,t+)  Vpp = (s+,t+)   (vertices: only Majorana non-resonant)
 //   fs = alpha_s_colfactor of the source bin
-NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k, double fs, const RowEdge &Rm,
+// SHARED: take the four t-channel ratio logarithms as sums of vertex/edge logarithms instead of
+// evaluating them.  lmp_in / lpm_in: ln(s-/s+) and ln(s+/s-) of the source bin if the caller has
+// them per column cell (NaN = evaluate here).
+template <bool SHARED>
+NUSI_HD void alpha_cell_mass_t(const PointParams &P, const PhiPhiTables *pp, int k, double fs, double lmp_in,
+                               double lpm_in, const RowEdge &Rm,
                              const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, const Vertex &Vmm,
                              const Vertex &Vpm, const Vertex &Vmp, const Vertex &Vpp, double &tot, int *warn) {
   const double mphi = P.mphi, g = P.g, Ga = P.Ga;
@@ -185,10 +269,19 @@ NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k
   const double gr = Ga / mphi;
   if (P.majorana) {
     /* t channel (u is identical for Majorana) */
-    const double LR1 = nlog(((1 + sm + tm) * (-1 + tp)) / ((-1 + tm) * (1 + sm + tp)));
-    const double LR2 = nlog(((1 + sp + tm) * (-1 + tp)) / ((-1 + tm) * (1 + sp + tp)));
-    const double LYm = nlog((sm * (1 + sp + tm)) / (sp * (1 + sm + tm)));
-    const double LYp = nlog((sm * (1 + sp + tp)) / (sp * (1 + sm + tp)));
+    double LR1, LR2, LYm, LYp;
+    if (SHARED) {  // the four ratio logarithms as sums of vertex and edge logarithms
+      const double dl = Rp.l1m - Rm.l1m, dc = Cm.ls - Cp.ls;
+      LR1 = Vmm.l1 + dl - Vmp.l1;
+      LR2 = Vpm.l1 + dl - Vpp.l1;
+      LYm = dc + Vpm.l1 - Vmm.l1;
+      LYp = dc + Vpp.l1 - Vmp.l1;
+    } else {
+      LR1 = nlog(((1 + sm + tm) * (-1 + tp)) / ((-1 + tm) * (1 + sm + tp)));
+      LR2 = nlog(((1 + sp + tm) * (-1 + tp)) / ((-1 + tm) * (1 + sp + tp)));
+      LYm = nlog((sm * (1 + sp + tm)) / (sp * (1 + sm + tm)));
+      LYp = nlog((sm * (1 + sp + tp)) / (sp * (1 + sm + tp)));
+    }
     const double N1 = sm * sp * (-tm + tp) * Cm.ls + sm * sp * (tm - tp) * Cp.ls - sm * sp * Vmm.l1 -
                       sm * sp * tp * Vmm.l1 + sm * sp * Vpm.l1 + sm * sp * tp * Vpm.l1 - sp * LR1 - sp * tm * LR1 -
                       sp * tp * LR1 - sp * tm * tp * LR1 + sm * sp * Vmp.lf + sm * sp * tm * Vmp.l1 + sm * LR2 +
@@ -224,7 +317,8 @@ NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k
       F_tm = -Vmm.dF + Vpm.dF;
     else
       F_tm = Vmm.dF - Vpm.dF + 0.5 * (sqr(Vmm.lq) - sqr(Vpm.lq));
-    const double lmp = nlog(sm / sp);
+    const double lmp = (lmp_in == lmp_in) ? lmp_in : nlog(sm / sp);
+    const double lpm = (lpm_in == lpm_in) ? lpm_in : nlog(sp / sm);
     a_tu = g4 / (32 * kPi * m4 * sm * sp * (1 + tm) * (1 + tp)) *
            (-4 * (sm - sp) * (1 + tm) * (tm - tp) * (1 + tp) + 2 * sm * sp * tp * (lmp - Vmm.l1 + Vpm.l1) +
             2 * sp * (1 + tm) * (1 + tp) * (Rm.l1m - Vmm.l1 - Rp.l1m + Vmp.l1) -
@@ -234,7 +328,7 @@ NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k
                 (Cm.l2s * (Cp.ls + Vmp.l1) - Cp.l2s * (Cm.ls + Vpp.l1) + Rp.l1m * (lmp - Vmp.l1 + Vpp.l1)) +
             sm * sp * (1 + tm) * (1 + tp) *
                 ((Cp.ls + Vmm.l1) * (Cm.ls2 + Rm.l1m - Rm.labs) + (Cm.ls + Vpm.l1) * (Cp.l2s - Rm.l1m + Rm.labs)) +
-            sm * sp * (nlog(sp / sm) + Vmp.l1 - Vpp.l1) * (2 * tm + (1 + tm) * (1 + tp) * Rp.labs) +
+            sm * sp * (lpm + Vmp.l1 - Vpp.l1) * (2 * tm + (1 + tm) * (1 + tp) * Rp.labs) +
             sm * sp * (1 + tm) * (1 + tp) * (Vmm.d2 - Vpm.d2 - Vmp.d2 + Vpp.d2) +
             sm * sp * (1 + tm) * (1 + tp) * (F_tp + F_tm));
     // NB: the reference's quadrature fallback for a negative alpha_tu assigns to a shadowing local
@@ -290,6 +384,12 @@ NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k
     *warn |= NUSI_WARN_ALPHA;
 }
 
+NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k, double fs, const RowEdge &Rm,
+                             const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, const Vertex &Vmm,
+                             const Vertex &Vpm, const Vertex &Vmp, const Vertex &Vpp, double &tot, int *warn) {
+  alpha_cell_mass_t<false>(P, pp, k, fs, NAN, NAN, Rm, Rp, Cm, Cp, Vmm, Vpm, Vmp, Vpp, tot, warn);
+}
+
 // One table entry computed from scratch (no sharing): used by the straightforward kernel and
 // by the host-side checks.  Em..Ep is the target bin (row), Emp..Epp the source bin (column).
 NUSI_HD double alpha_entry(const PointParams &P, const PhiPhiTables *pp, double Em, double Ep, double Emp, double Epp,
@@ -322,6 +422,35 @@ NUSI_HD double alpha_entry(const PointParams &P, const PhiPhiTables *pp, double 
       Cp.s = sp;
     }
     alpha_cell_mass(P, pp, k, fs, Rm, Rp, Cm, Cp, Vmm, Vpm, Vmp, Vpp, tot, warn);
+  }
+  return tot;
+}
+
+// same, through the shared-logarithm vertex (what the default tiled kernel computes)
+NUSI_HD double alpha_entry_shared(const PointParams &P, const PhiPhiTables *pp, double Em, double Ep, double Emp,
+                                  double Epp, int *warn) {
+  double tot = 0;
+  const double gr = P.Ga / P.mphi;
+  for (int k = 0; k < 3; ++k) {
+    RowEdge Rm, Rp;
+    ColEdge Cm, Cp;
+    Vertex Vmm, Vpm, Vmp, Vpp;
+    const double tm = t_of(P.mn[k], Em, P.mphi), tp = t_of(P.mn[k], Ep, P.mphi);
+    const double sm = s_of(P.mn[k], Emp, P.mphi), sp = s_of(P.mn[k], Epp, P.mphi);
+    const double fs = alpha_s_colfactor(P, sm, sp);
+    make_row_edge(tm, gr, true, Rm);
+    make_row_edge(tp, gr, true, Rp);
+    make_col_edge(sm, gr, true, Cm);
+    make_col_edge(sp, gr, true, Cp);
+    make_vertex_shared(Rm, Cm, gr, Vmm);
+    make_vertex_shared(Rm, Cp, gr, Vpm);
+    make_vertex_shared(Rp, Cm, gr, Vmp);
+    make_vertex_shared(Rp, Cp, gr, Vpp);
+#ifdef NUSI_HC_CELL_STRICT
+    alpha_cell_mass_t<false>(P, pp, k, fs, NAN, NAN, Rm, Rp, Cm, Cp, Vmm, Vpm, Vmp, Vpp, tot, warn);
+#else
+    alpha_cell_mass_t<true>(P, pp, k, fs, NAN, NAN, Rm, Rp, Cm, Cp, Vmm, Vpm, Vmp, Vpp, tot, warn);
+#endif
   }
   return tot;
 }

@@ -99,6 +99,7 @@ int nusi_opts_default(nusi_opts *o) {
   o->flav = 2;
   o->phiphi = 0;
   o->device = 0;
+  o->elementary_mode = 1;
   return NUSI_OK;
 }
 
@@ -232,7 +233,10 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
       cudaError_t e1 = upload(edge, &c->d_edgeE);
       if (e1 == cudaSuccess) e1 = upload(tiles, &c->d_tiles);
       if (e1 == cudaSuccess)
-        e1 = cudaFuncSetAttribute(alpha_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem));
+        e1 = cudaFuncSetAttribute(alpha_tile_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem));
+      if (e1 == cudaSuccess)
+        e1 = cudaFuncSetAttribute(alpha_tile_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem));
+
       if (e1 != cudaSuccess) {
         nusi_ctx_destroy(c);
         return fail(NUSI_E_CUDA, std::string("tile setup: ") + cudaGetErrorString(e1));
@@ -364,8 +368,14 @@ static int launch_xsec(nusi_ctx *c, const PointParams *d_params, int cnt, int *d
     dim3 ge((ntask + 127) / 128, cnt);
     edges_kernel<<<ge, 128, 0, s>>>(G, c->n_edges, d_params, c->d_edgeE, c->d_edges);
     dim3 gt(c->n_tiles, cnt);
-    alpha_tile_kernel<<<gt, 256, sizeof(TileSmem), s>>>(G, c->n_edges, d_params, c->d_edgeE, c->d_edges, c->d_tiles, c->d_tri,
-                                                       c->tstride, d_status);
+    const char *mode_env = getenv("NUSI_ALPHA_MODE");
+    const int mode = mode_env ? atoi(mode_env) : c->opt.elementary_mode;
+    if (mode == 0)
+      alpha_tile_kernel<0><<<gt, 256, sizeof(TileSmem), s>>>(G, c->n_edges, d_params, c->d_edgeE, c->d_edges, c->d_tiles,
+                                                            c->d_tri, c->tstride, d_status);
+    else
+      alpha_tile_kernel<1><<<gt, 256, sizeof(TileSmem), s>>>(G, c->n_edges, d_params, c->d_edgeE, c->d_edges, c->d_tiles,
+                                                            c->d_tri, c->tstride, d_status);
     c->n_launches += 1;
   } else {
     const long long nent = G.non_resonant ? (long long)G.NT * (G.NT - 1) / 2 : (long long)(G.NT - 1);

@@ -18,7 +18,9 @@ double hc_li3_neg(double x) { return nusi::li3_neg(x); }
 }
 
 #ifdef NUSI_HOSTCHECK_XSEC
+static int hc_shared_logs = 0;
 extern "C" {
+void hc_set_shared_logs(int on) { hc_shared_logs = on; }
 // lo/hi: the NT bin edges of the table rows (nuSIprop.hpp:223-233), built by the caller.
 void hc_tables(double mphi, double g, double Ga, const double *mn, const double *U2f, int majorana,
                int non_resonant, int phiphi, int NT, const double *lo, const double *hi, double *Gamma,
@@ -33,7 +35,9 @@ void hc_tables(double mphi, double g, double Ga, const double *mn, const double 
     if (alphaTilde) alphaTilde[i] = nusi::alphatilde_row(P, nullptr, lo[i], hi[i], warn);
     if (alpha)
       for (int m = i + 1; m < NT; ++m)
-        alpha[(size_t)i * NT + m] = nusi::alpha_entry(P, nullptr, lo[i], hi[i], lo[m], hi[m], warn);
+        alpha[(size_t)i * NT + m] = (majorana && non_resonant && hc_shared_logs)
+                                        ? nusi::alpha_entry_shared(P, nullptr, lo[i], hi[i], lo[m], hi[m], warn)
+                                        : nusi::alpha_entry(P, nullptr, lo[i], hi[i], lo[m], hi[m], warn);
   }
 }
 }
