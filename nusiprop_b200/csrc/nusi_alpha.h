@@ -244,12 +244,22 @@ NUSI_HD double alpha_pp_asymptotic(double sm, double sp, double tm, double tp) {
 //   Rm,Rp  row edges t-, t+      Cm,Cp  column edges s'-, s'+
 //   Vmm = (s-,t-)  Vpm = (s+,t-)  Vmp = (s-,t+)  Vpp = (s+,t+)   (vertices: only Majorana non-resonant)
 //   fs = alpha_s_colfactor of the source bin
-// SHARED: take the four t-channel ratio logarithms as sums of vertex/edge logarithms instead of
-// evaluating them.  lmp_in / lpm_in: ln(s-/s+) and ln(s+/s-) of the source bin if the caller has
-// them per column cell (NaN = evaluate here).
-template <bool SHARED>
-NUSI_HD void alpha_cell_mass_t(const PointParams &P, const PhiPhiTables *pp, int k, double fs, double lmp_in,
-                               double lpm_in, const RowEdge &Rm,
+// Logarithms of the t channel that belong to a cell EDGE rather than to the cell (two neighbouring
+// entries evaluate the same expression): computed here, or handed in by the tiled kernel.
+NUSI_HD double alpha_log_LR(double s, double tm, double tp) {  // nuSIprop.hpp:1284, "log(((1+s+t-)(-1+t+))/((-1+t-)(1+s+t+)))"
+  return nlog(((1 + s + tm) * (-1 + tp)) / ((-1 + tm) * (1 + s + tp)));
+}
+NUSI_HD double alpha_log_LY(double sm, double sp, double t) {  // nuSIprop.hpp:1284, "log((s-(1+s++t))/(s+(1+s-+t)))"
+  return nlog((sm * (1 + sp + t)) / (sp * (1 + sm + t)));
+}
+struct CellLogs {
+  double lmp, lpm;            // ln(s-/s+), ln(s+/s-)
+  double LR1, LR2, LYm, LYp;  // LR at s-, s+ ; LY at t-, t+
+};
+// HAVE_LOGS: take the six logarithms above from `L` instead of evaluating them.
+template <bool HAVE_LOGS>
+NUSI_HD void alpha_cell_mass_t(const PointParams &P, const PhiPhiTables *pp, int k, double fs, const CellLogs &L,
+                               const RowEdge &Rm,
                              const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, const Vertex &Vmm,
                              const Vertex &Vpm, const Vertex &Vmp, const Vertex &Vpp, double &tot, int *warn) {
   const double mphi = P.mphi, g = P.g, Ga = P.Ga;
@@ -270,17 +280,16 @@ NUSI_HD void alpha_cell_mass_t(const PointParams &P, const PhiPhiTables *pp, int
   if (P.majorana) {
     /* t channel (u is identical for Majorana) */
     double LR1, LR2, LYm, LYp;
-    if (SHARED) {  // the four ratio logarithms as sums of vertex and edge logarithms
-      const double dl = Rp.l1m - Rm.l1m, dc = Cm.ls - Cp.ls;
-      LR1 = Vmm.l1 + dl - Vmp.l1;
-      LR2 = Vpm.l1 + dl - Vpp.l1;
-      LYm = dc + Vpm.l1 - Vmm.l1;
-      LYp = dc + Vpp.l1 - Vmp.l1;
+    if (HAVE_LOGS) {
+      LR1 = L.LR1;
+      LR2 = L.LR2;
+      LYm = L.LYm;
+      LYp = L.LYp;
     } else {
-      LR1 = nlog(((1 + sm + tm) * (-1 + tp)) / ((-1 + tm) * (1 + sm + tp)));
-      LR2 = nlog(((1 + sp + tm) * (-1 + tp)) / ((-1 + tm) * (1 + sp + tp)));
-      LYm = nlog((sm * (1 + sp + tm)) / (sp * (1 + sm + tm)));
-      LYp = nlog((sm * (1 + sp + tp)) / (sp * (1 + sm + tp)));
+      LR1 = alpha_log_LR(sm, tm, tp);
+      LR2 = alpha_log_LR(sp, tm, tp);
+      LYm = alpha_log_LY(sm, sp, tm);
+      LYp = alpha_log_LY(sm, sp, tp);
     }
     const double N1 = sm * sp * (-tm + tp) * Cm.ls + sm * sp * (tm - tp) * Cp.ls - sm * sp * Vmm.l1 -
                       sm * sp * tp * Vmm.l1 + sm * sp * Vpm.l1 + sm * sp * tp * Vpm.l1 - sp * LR1 - sp * tm * LR1 -
@@ -317,8 +326,8 @@ NUSI_HD void alpha_cell_mass_t(const PointParams &P, const PhiPhiTables *pp, int
       F_tm = -Vmm.dF + Vpm.dF;
     else
       F_tm = Vmm.dF - Vpm.dF + 0.5 * (sqr(Vmm.lq) - sqr(Vpm.lq));
-    const double lmp = (lmp_in == lmp_in) ? lmp_in : nlog(sm / sp);
-    const double lpm = (lpm_in == lpm_in) ? lpm_in : nlog(sp / sm);
+    const double lmp = HAVE_LOGS ? L.lmp : nlog(sm / sp);
+    const double lpm = HAVE_LOGS ? L.lpm : nlog(sp / sm);
     a_tu = g4 / (32 * kPi * m4 * sm * sp * (1 + tm) * (1 + tp)) *
            (-4 * (sm - sp) * (1 + tm) * (tm - tp) * (1 + tp) + 2 * sm * sp * tp * (lmp - Vmm.l1 + Vpm.l1) +
             2 * sp * (1 + tm) * (1 + tp) * (Rm.l1m - Vmm.l1 - Rp.l1m + Vmp.l1) -
@@ -378,16 +387,16 @@ NUSI_HD void alpha_cell_mass_t(const PointParams &P, const PhiPhiTables *pp, int
   }
   tot += wgt * a_pp;
 
-  const double nrm = sqr(sqr(g / mphi));
-  if (warn && (a_s < 0 || a_t / nrm < -1e-11 || a_u / nrm < -1e-11 || a_tu / nrm < -1e-11 ||
-               (a_st + a_s + a_t) / nrm < -1e-11))
-    *warn |= NUSI_WARN_ALPHA;
+  // the reference tests x/(g/mphi)^4 < -1e-11 (nuSIprop.hpp:1505); same test without the divisions
+  const double lim = -1e-11 * sqr(sqr(g / mphi));
+  if (warn && (a_s < 0 || a_t < lim || a_u < lim || a_tu < lim || (a_st + a_s + a_t) < lim)) *warn |= NUSI_WARN_ALPHA;
 }
 
 NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k, double fs, const RowEdge &Rm,
                              const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, const Vertex &Vmm,
                              const Vertex &Vpm, const Vertex &Vmp, const Vertex &Vpp, double &tot, int *warn) {
-  alpha_cell_mass_t<false>(P, pp, k, fs, NAN, NAN, Rm, Rp, Cm, Cp, Vmm, Vpm, Vmp, Vpp, tot, warn);
+  CellLogs L;
+  alpha_cell_mass_t<false>(P, pp, k, fs, L, Rm, Rp, Cm, Cp, Vmm, Vpm, Vmp, Vpp, tot, warn);
 }
 
 // One table entry computed from scratch (no sharing): used by the straightforward kernel and
@@ -446,11 +455,8 @@ NUSI_HD double alpha_entry_shared(const PointParams &P, const PhiPhiTables *pp, 
     make_vertex_shared(Rm, Cp, gr, Vpm);
     make_vertex_shared(Rp, Cm, gr, Vmp);
     make_vertex_shared(Rp, Cp, gr, Vpp);
-#ifdef NUSI_HC_CELL_STRICT
-    alpha_cell_mass_t<false>(P, pp, k, fs, NAN, NAN, Rm, Rp, Cm, Cp, Vmm, Vpm, Vmp, Vpp, tot, warn);
-#else
-    alpha_cell_mass_t<true>(P, pp, k, fs, NAN, NAN, Rm, Rp, Cm, Cp, Vmm, Vpm, Vmp, Vpp, tot, warn);
-#endif
+    CellLogs L;
+    alpha_cell_mass_t<false>(P, pp, k, fs, L, Rm, Rp, Cm, Cp, Vmm, Vpm, Vmp, Vpp, tot, warn);
   }
   return tot;
 }
