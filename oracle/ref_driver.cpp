@@ -25,9 +25,52 @@
 #include <string>
 #include <chrono>
 #include <unistd.h>
+#ifdef NUSI_REF_ULP
+// Noise-floor ensemble member: the same unmodified reference, but every
+// result of log/log1p/exp/atan/atanh/carg/clog/cabs that the reference's own code obtains from libm is
+// moved by +-1 ulp for a deterministic quarter of the argument values.  How far the fluxes move under
+// this perturbation is how far two conforming libms can pull the reference apart.  The stand-in headers
+// are included BEFORE the macros so that only the reference's own call sites are affected.
+#include <gsl/gsl_linalg.h>
+#include <gsl/gsl_sf_dilog.h>
+#include <gsl/gsl_poly.h>
+#include "polylogarithm/src/cpp/Li2.hpp"
+#include "polylogarithm/src/cpp/Li3.hpp"
+#include <complex.h>
+#include <stdint.h>
+static inline double nusi_ulp(double v) {
+  uint64_t b;
+  std::memcpy(&b, &v, 8);
+  uint64_t h = b * 0x9E3779B97F4A7C15ull;
+  h ^= h >> 29;
+  const unsigned r = (unsigned)(h >> 40) & 7u;
+  if (r == 0) return nextafter(v, INFINITY);
+  if (r == 1) return nextafter(v, -INFINITY);
+  return v;
+}
+static inline double _Complex nusi_ulpc(double _Complex v) { return nusi_ulp(creal(v)) + I * nusi_ulp(cimag(v)); }
+#define log(x) nusi_ulp(log(x))
+#define log1p(x) nusi_ulp(log1p(x))
+#define exp(x) nusi_ulp(exp(x))
+#define atan(x) nusi_ulp(atan(x))
+#define atanh(x) nusi_ulp(atanh(x))
+#define carg(x) nusi_ulp(carg(x))
+#define cabs(x) nusi_ulp(cabs(x))
+#define clog(x) nusi_ulpc(clog(x))
+#endif
 #define private public
 #include "nuSIprop.hpp"
 #undef private
+#ifdef NUSI_REF_ULP
+#undef log
+#undef log1p
+#undef exp
+#undef atan
+#undef atanh
+#undef carg
+#undef cabs
+#undef clog
+#endif
 
 using nuSIprop::calculate_flux;
 
@@ -152,6 +195,9 @@ double nusi_ref_check_energy_conservation(double mphi, double g, double mntot, d
                                           double lEmin, double lEmax, double zmax, int flav) {
   calculate_flux ev(mphi, g, mntot, si, norm, majorana != 0, non_resonant != 0, normal_ordering != 0,
                     N_bins_E, lEmin, lEmax, zmax, flav, false);
+  // energy_FS() reads norm_total, which only evolve() sets (nuSIprop.hpp:205): call evolve() first,
+  // as every caller of the reference does, so the integral is not taken with an uninitialised member
+  ev.evolve();
   return ev.check_energy_conservation();
 }
 

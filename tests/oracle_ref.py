@@ -143,3 +143,20 @@ def relerr(a, b):
     r[np.isnan(a) & np.isnan(b)] = 0.0
     r[np.isnan(r)] = np.inf
     return r
+
+
+def noise_floor(ref, variants, halfwidth=8):
+    """Per-bin noise floor of the reference: largest relative spread between the strict oracle `ref`
+    [..., N] and its benign variants (FMA-contracted rebuild, +-1-ulp libm), taken over the leading
+    axes and widened to a running maximum over +-halfwidth neighbouring energy bins (one ensemble member
+    can agree by accident in a bin whose neighbours show the conditioning)."""
+    f = np.zeros(ref.shape[-1])
+    for v in variants:
+        r = relerr(v, ref)
+        f = np.maximum(f, r.reshape(-1, r.shape[-1]).max(axis=0))
+    return np.array([f[max(0, i - halfwidth): i + halfwidth + 1].max() for i in range(len(f))])
+
+
+def flux_tolerance(ref, variants, k=4.0, strict=1e-9):
+    """north_star's 1e-9 wherever the reference is self-consistent to that level, k x its own spread elsewhere."""
+    return np.maximum(strict, k * noise_floor(ref, variants))

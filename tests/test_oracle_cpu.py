@@ -1,0 +1,93 @@
+"""The oracle (unmodified reference + refshim) against every pinned number there is for this path:
+the reference's only shipped output (output/data_massless.txt, committed as a fixture), mpmath for
+the stand-ins of the absent third-party functions, and the committed golden fixtures."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = os.path.join(HERE, "golden")
+
+
+def _fmt(row):
+    return "%.5e  %.4e  %.4e  %.4e" % tuple(row)
+
+
+def test_kat_reference_shipped_output(oracle):
+    """test.py configuration (reference test.py:6-23) reproduces output/data_massless.txt row by row
+    at the precision the reference saved it with (%.4e)."""
+    mntot = float(0.0 + np.sqrt(7.42e-5) + np.sqrt(2.514e-3))
+    fm, ff, en = oracle.evolve(5e6, 1e-6, mntot, si=2.0, norm=6, majorana=True, non_resonant=False, normal_ordering=True,
+                               N_bins_E=100, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2, phiphi=False)
+    gold = np.loadtxt(os.path.join(GOLD, "reference_data_massless.txt"), skiprows=1)
+    assert gold.shape == (100, 4)
+    for j in range(100):
+        assert _fmt((en[j], ff[0, j], ff[1, j], ff[2, j])) == _fmt(gold[j])
+
+
+def test_golden_fixture_matches_shipped_output():
+    """The committed oracle fixture itself agrees with the reference's file (no oracle build needed)."""
+    z = np.load(os.path.join(GOLD, "oracle_flux.npz"))
+    gold = np.loadtxt(os.path.join(GOLD, "reference_data_massless.txt"), skiprows=1)
+    ff, en = z["testpy_massless/fla"], z["testpy_massless/E"]
+    for j in range(100):
+        assert _fmt((en[j], ff[0, j], ff[1, j], ff[2, j])) == _fmt(gold[j])
+
+
+def test_testcpp_config_tail_is_exact_zero(oracle):
+    """test.cpp defaults (E >= 1 GeV >> T = 6 MeV): a few tiny non-zero bins, then exact zeros."""
+    z = np.load(os.path.join(GOLD, "oracle_flux.npz"))
+    ff = z["testcpp_default/fla"]
+    nz = np.count_nonzero(ff[0])
+    assert 5 <= nz <= 20 and np.all(ff[:, nz:] == 0.0)
+    assert 1e-67 < ff[0, 0] < 1e-65
+
+
+def test_shim_special_functions_vs_mpmath(oracle):
+    g = json.load(open(os.path.join(GOLD, "specfun_mpmath.json")))
+    L = oracle.lib()
+    for x, v in g["li2_real"]:
+        got = L.nusi_ref_dilog(x)
+        assert abs(got - v) <= 8e-15 * max(abs(v), 1e-2), (x, got, v)
+    import ctypes as C
+    a, b = C.c_double(), C.c_double()
+    for x, y, re, im in g["cli2"]:
+        L.nusi_ref_cdilog(x, y, C.byref(a), C.byref(b))
+        assert abs(complex(a.value, b.value) - complex(re, im)) <= 8e-15 * max(abs(complex(re, im)), 1e-2), (x, y)
+    for x, v in g["li2_neg"]:
+        assert abs(L.nusi_ref_Li2(x) - v) <= 4e-16 * abs(v) + 1e-320
+    for x, v in g["li3_neg"]:
+        assert abs(L.nusi_ref_Li3(x) - v) <= 4e-16 * abs(v) + 1e-320
+
+
+def test_gsl_real_axis_convention(oracle):
+    """gsl_sf_complex_dilog_xy_e(x, 0.0): Im = -pi ln x for x >= 1, 0 below."""
+    import ctypes as C
+    L = oracle.lib()
+    a, b = C.c_double(), C.c_double()
+    L.nusi_ref_cdilog(3.0, 0.0, C.byref(a), C.byref(b))
+    assert b.value == pytest.approx(-np.pi * np.log(3.0), rel=1e-15)
+    L.nusi_ref_cdilog(0.5, 0.0, C.byref(a), C.byref(b))
+    assert b.value == 0.0
+    L.nusi_ref_cdilog(3.0, 1e-300, C.byref(a), C.byref(b))  # just above the cut: +pi ln x
+    assert b.value == pytest.approx(np.pi * np.log(3.0), rel=1e-12)
+
+
+def test_oracle_reproduces_committed_fixtures(oracle):
+    z = np.load(os.path.join(GOLD, "oracle_flux.npz"))
+    cases = json.load(open(os.path.join(GOLD, "oracle_flux_cases.json")))
+    for name in ("single_m100_g0.01_maj1_nr1_no1", "single_m30_g0.1_maj0_nr1_no0", "flav1_mn0.3_N60"):
+        c = dict(cases[name])
+        mphi, g, mntot = c.pop("mphi"), c.pop("g"), c.pop("mntot")
+        fm, ff, en = oracle.evolve(mphi, g, mntot, **c)
+        assert oracle.relerr(fm, z[name + "/mass"]).max() < 1e-12
+        assert oracle.relerr(ff, z[name + "/fla"]).max() < 1e-12
+
+
+def test_masses_anchor(oracle):
+    """mn at mntot = 0.1."""
+    mn = oracle.masses(0.1, True)
+    assert mn[0] == pytest.approx(0.021836889435201737, rel=1e-13)
+    assert oracle.masses(0.1, False)[2] == pytest.approx(0.00079530937968650967, rel=1e-11)
