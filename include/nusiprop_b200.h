@@ -85,6 +85,18 @@ int nusi_ctx_pmns2(const nusi_ctx *c, double *U2);
 /* The device-computed source term: out[(i-1)*N + j] = Lum(z[i], Emin[j], Emax[j]), i = 1..N_steps_z-1. */
 int nusi_ctx_source(const nusi_ctx *c, double *out);
 
+/* The same grids WITHOUT a context or a GPU (host arithmetic only): what the constructor of
+ * calculate_flux computes at nuSIprop.hpp:113-128.  Emin/Ecen/Emax are [N_bins_E] or NULL; the
+ * drop-in class uses this so that get_energy() works before the first evolve(). */
+int nusi_grid(int N_bins_E, double lEmin, double lEmax, double zmax, int *N_steps_z, double *zmax_eff,
+              double *Emin, double *Ecen, double *Emax);
+
+/* energy_FS() of the reference (nuSIprop.hpp:694-744 with flux_FS_E0 :666-692 and Lum_times_E
+ * :731-744): total energy of the free-streaming POWER-LAW flux, the quantity
+ * check_energy_conservation() (:339-357) compares the evolved flux with.  Host arithmetic
+ * (300 pow() calls); zmax_eff is the context's effective zmax (z[N_steps_z-1]). */
+int nusi_freestream_energy(double zmax_eff, double lEmin, double lEmax, double si, double norm, double *E_FS);
+
 /* Neutrino masses for one mntot: nuSIaux::getmL + nuSIprop.hpp:184-203.  Host arithmetic.
  * Returns NUSI_OK and mn[3], or NUSI_E_INVALID when the reference would exit(1). */
 int nusi_masses(double mntot, int normal_ordering, double mn[3]);

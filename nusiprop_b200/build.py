@@ -41,5 +41,32 @@ def build_library(force=False, verbose=False):
     return OUT
 
 
+ROOT = os.path.dirname(_HERE)
+CONSUMER = os.path.join(ROOT, "tests", "dropin", "_build", "consumer")
+CYTHON_DIR = os.path.join(_HERE, "cython")
+
+
+def build_dropin(force=False):
+    """Host-side consumers of the C ABI: the C++ consumer of the drop-in class (tests/dropin) and the
+    Cython wrapper nuSIprop.pyprop, both built in-tree so they travel to the GPU box."""
+    import glob
+    lib = build_library()
+    libdir = os.path.dirname(lib)
+    src = os.path.join(ROOT, "tests", "dropin", "consumer.cpp")
+    hdr = os.path.join(_HERE, "cxx", "nuSIprop.hpp")
+    deps = [src, hdr, os.path.join(ROOT, "include", "nusiprop_b200.h")]
+    if force or not os.path.exists(CONSUMER) or any(os.path.getmtime(d) > os.path.getmtime(CONSUMER) for d in deps):
+        os.makedirs(os.path.dirname(CONSUMER), exist_ok=True)
+        subprocess.check_call([os.environ.get("CXX", "g++"), "-std=c++11", "-O2", "-I", os.path.join(_HERE, "cxx"), "-I",
+                               os.path.join(ROOT, "include"), src, "-L", libdir, "-lnusiprop_b200", "-Wl,-rpath," + libdir,
+                               "-o", CONSUMER])
+    ext = glob.glob(os.path.join(CYTHON_DIR, "nuSIprop.*.so"))
+    cy_deps = deps[1:] + [os.path.join(CYTHON_DIR, f) for f in ("nuSIprop.pyx", "nuSIprop.pxd", "setup.py")]
+    if force or not ext or any(os.path.getmtime(d) > os.path.getmtime(ext[0]) for d in cy_deps):
+        subprocess.check_call([sys.executable, "setup.py", "-q", "build_ext", "--inplace"], cwd=CYTHON_DIR,
+                              stdout=subprocess.DEVNULL)
+    return CONSUMER
+
+
 if __name__ == "__main__":
     print(build_library(force="--force" in sys.argv, verbose=True))

@@ -293,6 +293,26 @@ int nusi_ctx_source(const nusi_ctx *c, double *out) {
   return NUSI_OK;
 }
 
+int nusi_grid(int N_bins_E, double lEmin, double lEmax, double zmax, int *N_steps_z, double *zmax_eff, double *Emin,
+              double *Ecen, double *Emax) {
+  if (N_bins_E < 2 || !(lEmax > lEmin) || !(zmax > 0)) return fail(NUSI_E_INVALID, "bad binning options");
+  HostGrid H;
+  build_grid(N_bins_E, lEmin, lEmax, zmax, true, H);
+  if (N_steps_z) *N_steps_z = H.Nz;
+  if (zmax_eff) *zmax_eff = H.zmax_eff;
+  const size_t b = (size_t)H.N * sizeof(double);
+  if (Emin) std::memcpy(Emin, H.Emin.data(), b);
+  if (Ecen) std::memcpy(Ecen, H.Ecen.data(), b);
+  if (Emax) std::memcpy(Emax, H.Emax.data(), b);
+  return NUSI_OK;
+}
+
+int nusi_freestream_energy(double zmax_eff, double lEmin, double lEmax, double si, double norm, double *E_FS) {
+  if (!E_FS || !(zmax_eff > 0) || !(lEmax > lEmin)) return NUSI_E_INVALID;
+  *E_FS = freestream_energy(zmax_eff, lEmin, lEmax, si, norm);
+  return NUSI_OK;
+}
+
 // host preparation of a batch: masses (cached per mntot), width, |U_fk|^2
 static void prepare_points(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
                            std::vector<PointParams> &pp, std::vector<int> &st) {

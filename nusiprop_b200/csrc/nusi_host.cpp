@@ -99,6 +99,36 @@ void build_grid(int N, double lEmin, double lEmax, double zmax, bool normal_orde
     for (int b = 0; b < 3; ++b) G.U2[a * 3 + b] = std::norm(U[a][b]);
 }
 
+// ---- free-streaming diagnostics (nuSIprop.hpp:666-744) -----------------------------------------
+// 100 panels x 3 Gauss-Legendre nodes in z.  flux_FS_E0: integrand (1+z)^-si SFR/H.  energy_FS:
+// integrand Lum_times_E(z, 10^lEmin, 10^lEmax)/H with the power-law source normalised by norm_total.
+template <typename F>
+static double gl3_panels(double z_min, double z_max, F integrand) {
+  const int n_panels = 100;  // N_integ_z, nuSIprop.hpp:550
+  double res = 0;
+  for (int f = 0; f < n_panels; f++) {
+    const double a = z_min + f * (z_max - z_min) / n_panels;
+    const double b = z_min + (f + 1.0) * (z_max - z_min) / n_panels;
+    const double z1 = (b - a) / 2. * gl_x(0) + (b + a) / 2., z2 = (b - a) / 2. * gl_x(1) + (b + a) / 2.,
+                 z3 = (b - a) / 2. * gl_x(2) + (b + a) / 2.;
+    res += (b - a) / 2. * (gl_w(0) * integrand(z1) + gl_w(1) * integrand(z2) + gl_w(2) * integrand(z3));
+  }
+  return res;
+}
+double freestream_energy(double zmax_eff, double lEmin, double lEmax, double si, double norm) {
+  const double E0 = 1e14;  // pivot energy, nuSIprop.hpp:549
+  const double fs0 = gl3_panels(0, zmax_eff, [&](double z) { return std::pow(1 + z, -si) * cosmo_SFR(z) / cosmo_H(z); });
+  const double norm_total = norm / fs0;
+  auto lum_times_E = [&](double z) {
+    const double Em = std::pow(10, lEmin), Ep = std::pow(10, lEmax);
+    if (std::fabs(si - 2) < 1e-5)
+      return norm_total * cosmo_SFR(z) * std::pow(E0 / (1 + z), si) *
+             (std::log(Ep / Em) + (2 - si) / 2.0 * (sqr(std::log(Ep)) - sqr(std::log(Em))));
+    return norm_total * cosmo_SFR(z) * std::pow(E0 / (1 + z), si) * (std::pow(Ep, 2 - si) - std::pow(Em, 2 - si)) / (2 - si);
+  };
+  return gl3_panels(0, zmax_eff, [&](double z) { return lum_times_E(z) / cosmo_H(z); });
+}
+
 double scalar_width(double mphi, double g, bool majorana) {
   if (majorana) return sqr(g) * mphi / (16.0 * M_PI);
   return sqr(g) * mphi / (8.0 * M_PI);

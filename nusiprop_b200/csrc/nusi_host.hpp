@@ -36,6 +36,9 @@ bool solve_masses(double mntot, bool normal_ordering, double mn[3]);
 // scalar_width (nuSIprop.hpp:748-757)
 double scalar_width(double mphi, double g, bool majorana);
 
+// free-streaming diagnostics: energy_FS (nuSIprop.hpp:694-744) for norm_total = norm / flux_FS_E0 (:205, :666-692)
+double freestream_energy(double zmax_eff, double lEmin, double lEmax, double si, double norm);
+
 // phi-phi tables: binary loader (interp.hpp:249-292) + contraction of the log10(delta) axis.
 struct HostPhiPhi {
   std::vector<double> at_x0, at_f;        // ln|tbar+| nodes, contracted values
