@@ -129,6 +129,18 @@ int nusi_evolve_points(nusi_ctx *c, const nusi_points *p, double *d_flux_mass, d
 int nusi_tables_batch(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
                       double *Gamma, double *alphaTilde, double *alpha, int *status);
 
+/* Generator of the two phi-phi cross-section tables in the reference's binary format (records of
+ * float32 (x_0, .., x_{D-1}, f), last coordinate fastest: interp.hpp:259-290, xsec/text_to_binary.cpp).
+ * Replaces xsec/funcs.c:12-39 (integrand) + xsec/tables_phiphi.py:21-59 (scipy dblquad per node, days
+ * on a CPU) by fixed Gauss-Legendre quadrature in a CUDA kernel (seconds).  Node grids as the script:
+ *   alphatilde: |tbar_plus| = geomspace(4, 1e4, n_t)  x  log10 delta = linspace(0.005, 0.05, n_d)
+ *   alpha:      sbar_plus   = geomspace(4, 1e4, n_s)  x  n = 1..n_n  x  log10 delta (same)
+ * Pass 0 for a count to get the reference's sizes (n_t 5000, n_s 1000, n_n 1000, n_d 100: the only
+ * sizes the reference's own constructor can load, nuSIprop.hpp:168-169; alpha file = 1.6 GB).  Either
+ * path may be NULL to skip that table.  seconds (may be NULL) receives the CUDA-event time of the kernels. */
+int nusi_phiphi_tables_generate(int device, const char *alphatilde_path, const char *alpha_path, int n_t, int n_s,
+                                int n_n, int n_d, double *seconds);
+
 /* CUDA-event time of the last nusi_evolve_points / nusi_evolve_batch on this context, per kernel,
  * summed over its launches [ms]: Gamma/alphaTilde rows, alpha table, z-stepping integrator; and
  * how many kernels were launched.  Blocks until that work has finished. */

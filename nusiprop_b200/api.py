@@ -174,6 +174,19 @@ def evolve_scan(mphi, g, mntot, **ctx_kwargs):
         ctx.close()
 
 
+def generate_phiphi_tables(alphatilde_path, alpha_path, n_t=0, n_s=0, n_n=0, n_d=0, device=0):
+    """Write the two phi-phi cross-section tables in the reference's binary format with the CUDA generator
+    (replaces reference xsec/funcs.c + tables_phiphi.py + text_to_binary.cpp).  Zero counts = the
+    reference's sizes (5000 x 100 and 1000 x 1000 x 100: a 6 MB and a 1.6 GB file).  Either path may be
+    None.  Returns the CUDA-event seconds spent in the generator kernels."""
+    lib = _lib.load()
+    sec = C.c_double()
+    check(lib.nusi_phiphi_tables_generate(int(device), alphatilde_path.encode() if alphatilde_path else None,
+                                          alpha_path.encode() if alpha_path else None, int(n_t), int(n_s), int(n_n), int(n_d),
+                                          C.byref(sec)), "nusi_phiphi_tables_generate")
+    return sec.value
+
+
 def specfun(which, x, y=None, device=0):
     """Device special functions (unit tests): 0 Re Li2, 1 complex Li2, 2 Li2 on [-1,0], 3 Li3 on [-1,0]."""
     lib = _lib.load()

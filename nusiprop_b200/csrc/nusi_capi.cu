@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <array>
 #include <map>
 #include <string>
@@ -591,6 +592,115 @@ int nusi_last_timing(const nusi_ctx *c, float *ms_rows, float *ms_alpha, float *
   if (ms_integrate) *ms_integrate = ti;
   if (n_launches) *n_launches = c->n_launches;
   return NUSI_OK;
+}
+
+// coordinates go through the reference pipeline's text step ("%.7e", tables_phiphi.py:36,59) before
+// they become float32 (text_to_binary.cpp:32); the node VALUE is computed at the unrounded double
+static float text_rounded(double v) {
+  char buf[64];
+  std::snprintf(buf, sizeof buf, "%.7e", v);
+  return std::strtof(buf, nullptr);
+}
+static std::vector<double> geomspace(double a, double b, int n) {
+  std::vector<double> v(n);
+  const double la = std::log10(a), lb = std::log10(b);
+  for (int i = 0; i < n; ++i) v[i] = std::pow(10.0, la + (lb - la) * i / (n - 1));
+  v[0] = a;
+  v[n - 1] = b;
+  return v;
+}
+static std::vector<double> linspace(double a, double b, int n) {
+  std::vector<double> v(n);
+  for (int i = 0; i < n; ++i) v[i] = a + (b - a) * i / (n - 1);
+  v[n - 1] = b;
+  return v;
+}
+
+// one table: kernel in slabs of <= 2^24 nodes, records interleaved on the host and appended to the file
+static int generate_table(int which, const char *path, const std::vector<double> &x0, const std::vector<double> &x1,
+                          const std::vector<double> &x2, float *ms_total) {
+  const int D = which == 0 ? 2 : 3;
+  const long long n0 = (long long)x0.size(), n1 = (long long)x1.size(), n2 = which == 0 ? 1 : (long long)x2.size();
+  const long long total = n0 * n1 * n2;
+  FILE *fp = std::fopen(path, "wb");
+  if (!fp) return fail(NUSI_E_TABLE, std::string("cannot open ") + path + " for writing");
+  double *d_x[3] = {nullptr, nullptr, nullptr};
+  float *d_out = nullptr;
+  const long long slab = 1LL << 24;
+  cudaError_t e = upload(x0, &d_x[0]);
+  if (e == cudaSuccess) e = upload(x1, &d_x[1]);
+  if (e == cudaSuccess && which == 1) e = upload(x2, &d_x[2]);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&d_out, (size_t)slab * sizeof(float));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (e == cudaSuccess) e = cudaEventCreate(&e0);
+  if (e == cudaSuccess) e = cudaEventCreate(&e1);
+  std::vector<float> vals((size_t)slab), rec((size_t)slab * (D + 1));
+  std::vector<float> c0(n0), c1(n1), c2(n2);
+  for (long long i = 0; i < n0; ++i) c0[i] = text_rounded(x0[i]);
+  for (long long i = 0; i < n1; ++i) c1[i] = which == 0 ? text_rounded(x1[i]) : (float)x1[i];  // "%4u" for n
+  for (long long i = 0; i < n2 && which == 1; ++i) c2[i] = text_rounded(x2[i]);
+  bool io_ok = true;
+  for (long long first = 0; first < total && e == cudaSuccess && io_ok; first += slab) {
+    const long long cnt = std::min(slab, total - first);
+    cudaEventRecord(e0);
+    phiphi_table_kernel<<<(unsigned)((cnt + 127) / 128), 128>>>(which, first, cnt, (int)n1, (int)n2, d_x[0], d_x[1], d_x[2], d_out);
+    cudaEventRecord(e1);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpy(vals.data(), d_out, (size_t)cnt * sizeof(float), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) break;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    *ms_total += ms;
+    for (long long i = 0; i < cnt; ++i) {
+      const long long node = first + i;
+      float *r = &rec[(size_t)i * (D + 1)];
+      if (which == 0) {
+        r[0] = c0[node / n1];
+        r[1] = c1[node % n1];
+        r[2] = vals[i];
+      } else {
+        const long long i01 = node / n2;
+        r[0] = c0[i01 / n1];
+        r[1] = c1[i01 % n1];
+        r[2] = c2[node % n2];
+        r[3] = vals[i];
+      }
+    }
+    io_ok = std::fwrite(rec.data(), sizeof(float) * (D + 1), (size_t)cnt, fp) == (size_t)cnt;
+  }
+  io_ok = (std::fclose(fp) == 0) && io_ok;
+  for (double *p : d_x)
+    if (p) cudaFree(p);
+  if (d_out) cudaFree(d_out);
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
+  if (e != cudaSuccess) return fail(NUSI_E_CUDA, std::string("phiphi_table_kernel: ") + cudaGetErrorString(e));
+  if (!io_ok) return fail(NUSI_E_TABLE, std::string("short write on ") + path);
+  return NUSI_OK;
+}
+
+int nusi_phiphi_tables_generate(int device, const char *alphatilde_path, const char *alpha_path, int n_t, int n_s,
+                                int n_n, int n_d, double *seconds) {
+  if (n_t == 0) n_t = 5000;
+  if (n_s == 0) n_s = 1000;
+  if (n_n == 0) n_n = 1000;
+  if (n_d == 0) n_d = 100;
+  if (n_t < 4 || n_s < 4 || n_n < 4 || n_d < 4) return fail(NUSI_E_INVALID, "phi-phi tables need at least 4 nodes per axis");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+    return fail(NUSI_E_NO_DEVICE, "no CUDA device");
+  CU(cudaSetDevice(device));
+  float ms = 0;
+  int rc = NUSI_OK;
+  const std::vector<double> l10d = linspace(0.005, 0.05, n_d);
+  if (alphatilde_path) rc = generate_table(0, alphatilde_path, geomspace(4.0, 1e4, n_t), l10d, std::vector<double>(), &ms);
+  if (rc == NUSI_OK && alpha_path) {
+    std::vector<double> nn(n_n);
+    for (int i = 0; i < n_n; ++i) nn[i] = i + 1;
+    rc = generate_table(1, alpha_path, geomspace(4.0, 1e4, n_s), nn, l10d, &ms);
+  }
+  if (seconds) *seconds = ms * 1e-3;
+  return rc;
 }
 
 int nusi_specfun_eval(int device, int which, int n, const double *x, const double *y, double *re, double *im) {

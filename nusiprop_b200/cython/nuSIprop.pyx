@@ -4,7 +4,7 @@
 keywords and defaults, and methods as the reference's nuSIprop.pyx (:12-144).  Added: evolve_scan(),
 one call for many (mphi, g, mntot) points, and getters that fill whole arrays instead of one
 element per call."""
-from nuSIprop cimport calculate_flux, evolve_scan as _c_evolve_scan
+from nuSIprop cimport calculate_flux, c_evolve_scan
 import numpy as np
 cimport numpy as cnp
 import warnings
@@ -114,7 +114,7 @@ def evolve_scan(mphi, g, mntot, bint majorana=True, bint non_resonant=True, bint
     cdef cnp.ndarray[double, ndim=3] ff = np.empty((n, 3, N_bins_E))
     cdef cnp.ndarray[int, ndim=1] st = np.zeros(n, dtype=np.intc)
     cdef int rc
-    rc = _c_evolve_scan(n, &vm[0], &vg[0], &vn[0], &fm[0, 0, 0], &ff[0, 0, 0], &st[0], majorana, non_resonant,
+    rc = c_evolve_scan(n, &vm[0], &vg[0], &vn[0], &fm[0, 0, 0], &ff[0, 0, 0], &st[0], majorana, non_resonant,
                         normal_ordering, N_bins_E, lEmin, lEmax, zmax, flav, phiphi)
     if rc != 0:
         raise RuntimeError("nuSIprop.evolve_scan failed with code %d" % rc)

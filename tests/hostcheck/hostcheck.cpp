@@ -17,6 +17,13 @@ double hc_li2_neg(double x) { return nusi::li2_neg(x); }
 double hc_li3_neg(double x) { return nusi::li3_neg(x); }
 }
 
+#include "nusi_phiphi_gen.h"
+extern "C" {
+double hc_pp_integrand(double s, double t) { return nusi::pp_integrand(s, t); }
+double hc_pp_alpha_node(double splus, double n, double l10d) { return nusi::pp_alpha_node(splus, n, l10d); }
+double hc_pp_alphatilde_node(double abs_tplus, double l10d) { return nusi::pp_alphatilde_node(abs_tplus, l10d); }
+}
+
 #ifdef NUSI_HOSTCHECK_XSEC
 static int hc_shared_logs = 0;
 extern "C" {
