@@ -18,6 +18,6 @@ cdef extern from "nuSIprop.hpp" namespace "nuSIprop":
 
         double mphi, g, mntot, si, norm
 
-    int c_evolve_scan "evolve_scan"(int n, const double *mphi, const double *g, const double *mntot, double *flux_mass,
+    int c_evolve_scan "nuSIprop::evolve_scan"(int n, const double *mphi, const double *g, const double *mntot, double *flux_mass,
                                     double *flux_fla, int *status, bint majorana, bint non_resonant, bint normal_ordering,
                     int N_bins_E, double lEmin, double lEmax, double zmax, int flav, bint phiphi) except +
