@@ -56,10 +56,13 @@ typedef struct nusi_opts {
   const char *alpha_phiphi_path;      /* NULL -> "xsec/alpha_phiphi.bin"      (nuSIprop.hpp:169) */
   int device;            /* CUDA device ordinal, default 0 */
   int max_points_per_launch; /* 0 = choose from free HBM */
-  int elementary_mode;   /* alpha builder (Majorana, non_resonant): 0 = strict, every log/arg evaluated where the
-                            reference evaluates it; 1 (default) = the logs/args of a table vertex are formed from
-                            one vertex log plus per-edge logs (same closed forms, ~1.6x faster; parity with the
-                            reference stays at the reference's own FMA-on/off noise floor) */
+  int elementary_mode;   /* alpha builder (Majorana, non_resonant):
+                            0 = strict: every log/arg evaluated where the reference evaluates it;
+                            1 = the logs/args of a table vertex are formed from one vertex log plus per-edge logs;
+                            2 (default) = 1 + per-vertex grouping of the s-t / t-u interference sums, 16x16-vertex
+                                tiles, all three target masses per barrier (same closed forms; fastest).
+                            Parity with the reference is at the reference's own FMA-on/off noise floor in all
+                            three modes. */
 } nusi_opts;
 
 /* Fills *o with the reference's C++ constructor defaults (nuSIprop.hpp:61-65). */

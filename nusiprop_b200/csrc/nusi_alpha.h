@@ -176,6 +176,73 @@ NUSI_HD void make_vertex_shared(const RowEdge &R, const ColEdge &C, double gr, V
   V.ca = C.args + R.phi - kPi;
 }
 
+// ---- compact vertex -----------------------------------------------------------------------
+// The closed forms use the vertex data only through three numbers per vertex:
+//   l1 = ln(1+s+t)
+//   G  = everything of the s-t interference that belongs to ONE vertex (nuSIprop.hpp:1452-1464: the two
+//        dilogarithms, the arg term and the  l1*(...)  term), so that  alpha_st ~ G-- - G+- - G-+ + G++ + edge terms
+//   H  = Li2((1+s+t)/(2+s)) - K,  K = dF (t < -1) or -dF - lq^2/2 (t >= -1), so that the dilogarithm part of the
+//        t-u interference (nuSIprop.hpp:1373-1399) is  H-- - H+- - H-+ + H++
+// (signs: first index s'-/s'+, second t-/t+).  Same logarithms as make_vertex_shared(); the case splits of the
+// dilogarithm reductions are decided by products instead of quotients (no division in a vertex).
+struct VertexC {
+  double l1, G, H;
+};
+NUSI_HD void make_vertex_compact(const RowEdge &R, const ColEdge &C, double gr, VertexC &V) {
+  const double s = C.s, t = R.t;
+  const double one_st = 1 + s + t, d = 1 + t;
+  const double l1 = nlog1p(s + t);
+  V.l1 = l1;
+  // FCTR dilogarithm and the squared logarithm that goes with it
+  double K;
+  if (t < -1) {
+    const double lnx = l1 - C.ls, ln1mx = R.labs - C.ls;  // x = (1+s+t)/s
+    K = (one_st <= 0.5 * s) ? li2_from_u(-ln1mx) : kZeta2 - lnx * ln1mx - li2_from_u(-lnx);
+  } else {
+    const double lnx = C.ls - l1, ln1mx = R.labs - l1;  // x = s/(1+s+t)
+    const double dF = (s <= 0.5 * one_st) ? li2_from_u(-ln1mx) : kZeta2 - lnx * ln1mx - li2_from_u(-lnx);
+    K = -dF - 0.5 * sqr(l1 - C.ls);
+  }
+  {
+    const double lnx = l1 - C.l2, ln1mx = R.l1m - C.l2;  // x = (1+s+t)/(2+s)
+    const double d2 = (one_st <= 0.5 * (2 + s)) ? li2_from_u(-ln1mx) : kZeta2 - lnx * ln1mx - li2_from_u(-lnx);
+    V.H = d2 - K;
+  }
+  // real-axis dilogarithm of zr = (1+s+t)/(1+t) = 1 + s/d with GSL's imaginary part
+  const double lnzr = l1 - R.labs;
+  double zr_re, zr_im;
+  if (d > 0) {  // zr > 1
+    zr_re = (s > d) ? 2.0 * kZeta2 - 0.5 * lnzr * lnzr - li2_from_u(l1 - C.ls)
+                    : kZeta2 - lnzr * (C.ls - R.labs) - li2_from_u(-lnzr);
+    zr_im = -kPi * lnzr;
+  } else {  // zr < 0 (1+s+t > 0 for every vertex of the table)
+    zr_re = (s > -2.0 * d) ? -kZeta2 - 0.5 * lnzr * lnzr - li2_from_u(l1 - C.ls) : li2_from_u(R.labs - C.ls);
+    zr_im = 0.0;
+  }
+  // complex dilogarithm of zc = (1+s+t)/(2 - i ga + t): |zc|^2 = (1+s+t)^2/D, Re zc = (1+s+t)(2+t)/D
+  const double D = sqr(2 + t) + sqr(gr);
+  const bool inv = sqr(one_st) > D;
+  const bool refl = inv ? ((2 + t) > 0.5 * one_st) : (one_st * (2 + t) > 0.5 * D);
+  const double lnr = l1 - 0.5 * R.lnD;
+  const double lnw = inv ? -lnr : lnr, argw = inv ? -R.phi : R.phi;
+  const double lnomw = inv ? 0.5 * C.lnN - l1 : 0.5 * (C.lnN - R.lnD);
+  const double argomw = inv ? C.args : C.args - kPi + R.phi;
+  cplx res;
+  if (refl) {
+    const cplx tt = li2_from_u_cplx(mk(-lnw, -argw));
+    res = mk(-tt.re + kZeta2 - lnw * lnomw + argw * argomw, -tt.im - argw * lnomw - argomw * lnw);
+  } else {
+    res = li2_from_u_cplx(mk(-lnomw, -argomw));
+  }
+  if (inv) {
+    const double lim = R.phi - kPi;
+    res = mk(-res.re - 0.5 * (lnr * lnr - lim * lim) - kZeta2, -res.im - lnr * lim);
+  }
+  const double ca = C.args + R.phi - kPi;
+  V.G = 2 * gr * (zr_im - res.im) - 2 * (zr_re - res.re) + 2 * gr * (R.argn - ca) * l1 +
+        l1 * (C.lam - R.lam2 - 2 * (C.ls - R.lfabs));
+}
+
 // 3x3 Gauss-Legendre fallback on  y in [t+, t-], x in [s-, s+]  (nuSIprop.hpp:1288-1303 etc.)
 // KIND 0: t and u propagators (Majorana t), 1: single propagator (Dirac t, u), 2: t-u interference
 template <int KIND>
@@ -392,6 +459,74 @@ NUSI_HD void alpha_cell_mass_t(const PointParams &P, const PhiPhiTables *pp, int
   if (warn && (a_s < 0 || a_t < lim || a_u < lim || a_tu < lim || (a_st + a_s + a_t) < lim)) *warn |= NUSI_WARN_ALPHA;
 }
 
+// Majorana non-resonant table entry from compact vertices.  Same closed forms and term order as
+// alpha_cell_mass_t<true>; the vertex sums Gs = G-- - G+- - G-+ + G++ and Hs (same signs) replace the
+// per-field sums.  l1xy: x = s'-/s'+ (m/p), y = t-/t+ (m/p).
+NUSI_HD void alpha_cell_mass_compact(const PointParams &P, const PhiPhiTables *pp, int k, double fs, const CellLogs &L,
+                                     const RowEdge &Rm, const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, double l1mm,
+                                     double l1pm, double l1mp, double l1pp, double Gs, double Hs, double &tot, int *warn) {
+  const double mphi = P.mphi, g = P.g, Ga = P.Ga;
+  const double g4 = sqr(sqr(g)), m4 = sqr(sqr(mphi));
+  const double U2 = P.U2f[k];
+  const double wgt = m4 / (2 * P.mn[k]);
+  const double tm = Rm.t, tp = Rp.t, sm = Cm.s, sp = Cp.s;
+  const double gr = Ga / mphi;
+
+  double a_s = g4 / (8 * kPi * Ga * cub(mphi)) * (tm - tp) * fs;
+  a_s *= U2;
+  tot += wgt * a_s;
+
+  const double LR1 = L.LR1, LR2 = L.LR2, LYm = L.LYm, LYp = L.LYp;
+  const double N1 = sm * sp * (-tm + tp) * Cm.ls + sm * sp * (tm - tp) * Cp.ls - sm * sp * l1mm - sm * sp * tp * l1mm +
+                    sm * sp * l1pm + sm * sp * tp * l1pm - sp * LR1 - sp * tm * LR1 - sp * tp * LR1 - sp * tm * tp * LR1 +
+                    sm * sp * l1mp + sm * sp * tm * l1mp + sm * LR2 + sm * tm * LR2 + sm * tp * LR2 + sm * tm * tp * LR2 -
+                    sm * sp * l1pp - sm * sp * tm * l1pp;
+  double a_t = g4 / (sm * sp * 16 * kPi * m4) *
+               (-((sm - sp) * (3 + 2 * tm * (-1 + tp) - 2 * tp) * (tm - tp)) / ((-1 + tm) * (-1 + tp)) +
+                2 * (N1) / ((1 + tm) * (1 + tp)) -
+                ((sm * sp * LYm) / sqr(1 + tm) + (((sm - sp) * (tm - tp) * (1 + tp)) / (1 + tm) - sm * sp * LYp) / sqr(1 + tp)));
+  if (a_t < 0) a_t = alpha_gl2d<0>(tp, tm, sm, sp) * (g4 / (16 * kPi * m4));
+  a_t *= U2;
+  tot += wgt * a_t;
+  tot += wgt * a_t;  // u channel = t channel for Majorana
+
+  const double lmp = L.lmp, lpm = L.lpm;
+  double a_tu = g4 / (32 * kPi * m4 * sm * sp * (1 + tm) * (1 + tp)) *
+                (-4 * (sm - sp) * (1 + tm) * (tm - tp) * (1 + tp) + 2 * sm * sp * tp * (lmp - l1mm + l1pm) +
+                 2 * sp * (1 + tm) * (1 + tp) * (Rm.l1m - l1mm - Rp.l1m + l1mp) -
+                 2 * sm * (1 + tm) * (1 + tp) * (Rm.l1m - l1pm - Rp.l1m + l1pp) + 2 * sm * sp * (-l1mm + l1pm + l1mp - l1pp) +
+                 sm * sp * (1 + tm) * (1 + tp) *
+                     (Cm.l2s * (Cp.ls + l1mp) - Cp.l2s * (Cm.ls + l1pp) + Rp.l1m * (lmp - l1mp + l1pp)) +
+                 sm * sp * (1 + tm) * (1 + tp) *
+                     ((Cp.ls + l1mm) * (Cm.ls2 + Rm.l1m - Rm.labs) + (Cm.ls + l1pm) * (Cp.l2s - Rm.l1m + Rm.labs)) +
+                 sm * sp * (lpm + l1mp - l1pp) * (2 * tm + (1 + tm) * (1 + tp) * Rp.labs) + sm * sp * (1 + tm) * (1 + tp) * Hs);
+  a_tu *= U2;
+  tot += wgt * a_tu;
+
+  const double dS = 2 * (tm - tp) + (Rm.l1m - Rp.l1m);
+  double a_st = g4 / (32 * kPi * (1 + sqr(gr)) * m4) *
+                (Gs + 2 * (gr * Cm.args - gr * Cp.args + Cp.lam / 2. - Cm.lam / 2. + Cm.ls - Cp.ls) * dS);
+  a_st *= U2;
+  tot += wgt * a_st;
+  tot += wgt * a_st;  // s-u interference = s-t for Majorana
+
+  double a_pp = 0;
+  if ((sm > 4) && P.phiphi) {
+    if (sm < 1e4) {
+      const double delta = sp / sm;
+      a_pp = g4 / m4 * fabs(phiphi_alpha_eval(pp, sm, nlog(-sm / tm) / nlog(delta) * 1.0001, log10(delta), warn));
+    } else {
+      a_pp = g4 / m4 * alpha_pp_asymptotic(sm, sp, tm, tp);
+    }
+    a_pp *= U2;
+    a_pp *= 8;  // x2 targets, x2 neutrinos, x2 Majorana (nuSIprop.hpp:1494-1501)
+  }
+  tot += wgt * a_pp;
+
+  const double lim = -1e-11 * sqr(sqr(g / mphi));
+  if (warn && (a_s < 0 || a_t < lim || a_tu < lim || (a_st + a_s + a_t) < lim)) *warn |= NUSI_WARN_ALPHA;
+}
+
 NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k, double fs, const RowEdge &Rm,
                              const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, const Vertex &Vmm,
                              const Vertex &Vpm, const Vertex &Vmp, const Vertex &Vpp, double &tot, int *warn) {
@@ -457,6 +592,38 @@ NUSI_HD double alpha_entry_shared(const PointParams &P, const PhiPhiTables *pp, 
     make_vertex_shared(Rp, Cp, gr, Vpp);
     CellLogs L;
     alpha_cell_mass_t<false>(P, pp, k, fs, L, Rm, Rp, Cm, Cp, Vmm, Vpm, Vmp, Vpp, tot, warn);
+  }
+  return tot;
+}
+
+// same, through compact vertices (what the default tiled kernel computes)
+NUSI_HD double alpha_entry_compact(const PointParams &P, const PhiPhiTables *pp, double Em, double Ep, double Emp,
+                                   double Epp, int *warn) {
+  double tot = 0;
+  const double gr = P.Ga / P.mphi;
+  for (int k = 0; k < 3; ++k) {
+    RowEdge Rm, Rp;
+    ColEdge Cm, Cp;
+    VertexC Vmm, Vpm, Vmp, Vpp;
+    const double tm = t_of(P.mn[k], Em, P.mphi), tp = t_of(P.mn[k], Ep, P.mphi);
+    const double sm = s_of(P.mn[k], Emp, P.mphi), sp = s_of(P.mn[k], Epp, P.mphi);
+    make_row_edge(tm, gr, true, Rm);
+    make_row_edge(tp, gr, true, Rp);
+    make_col_edge(sm, gr, true, Cm);
+    make_col_edge(sp, gr, true, Cp);
+    make_vertex_compact(Rm, Cm, gr, Vmm);
+    make_vertex_compact(Rm, Cp, gr, Vpm);
+    make_vertex_compact(Rp, Cm, gr, Vmp);
+    make_vertex_compact(Rp, Cp, gr, Vpp);
+    CellLogs L;
+    L.lmp = nlog(sm / sp);
+    L.lpm = nlog(sp / sm);
+    L.LR1 = alpha_log_LR(sm, tm, tp);
+    L.LR2 = alpha_log_LR(sp, tm, tp);
+    L.LYm = alpha_log_LY(sm, sp, tm);
+    L.LYp = alpha_log_LY(sm, sp, tp);
+    alpha_cell_mass_compact(P, pp, k, alpha_s_colfactor(P, sm, sp), L, Rm, Rp, Cm, Cp, Vmm.l1, Vpm.l1, Vmp.l1, Vpp.l1,
+                            Vmm.G - Vpm.G - Vmp.G + Vpp.G, Vmm.H - Vpm.H - Vmp.H + Vpp.H, tot, warn);
   }
   return tot;
 }

@@ -48,6 +48,9 @@ struct nusi_ctx {
   double *d_edgeE = nullptr;  // distinct bin-edge energies of the table cells (tiled builder)
   int2 *d_tiles = nullptr;
   int n_tiles = 0;
+  int2 *d_ctiles = nullptr;  // compact builder: (segment a, segment b) pairs and the segment boundaries
+  int *d_seg = nullptr;
+  int n_ctiles = 0;
   int n_edges = 0;
   bool use_tiles = false;
   double *d_edges = nullptr;  // per-launch edge blocks [cap_points][edge_block_doubles]
@@ -100,7 +103,7 @@ int nusi_opts_default(nusi_opts *o) {
   o->flav = 2;
   o->phiphi = 0;
   o->device = 0;
-  o->elementary_mode = 1;
+  o->elementary_mode = 2;
   return NUSI_OK;
 }
 
@@ -116,6 +119,8 @@ void nusi_ctx_destroy(nusi_ctx *c) {
                     c->d_zsrc, c->d_rsn, c->d_pp[0], c->d_pp[1], c->d_pp[2], c->d_pp[3], c->d_pp[4],
                     c->d_rows, c->d_tri, c->d_work, c->d_edgeE, c->d_edges};
   if (c->d_tiles) cudaFree(c->d_tiles);
+  if (c->d_ctiles) cudaFree(c->d_ctiles);
+  if (c->d_seg) cudaFree(c->d_seg);
   for (double *p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
@@ -231,8 +236,22 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
       const int nt = (H.NT + NUSI_TS - 1) / NUSI_TS;
       for (int tb = 0; tb < nt; ++tb)
         for (int ta = 0; ta <= tb; ++ta) tiles.push_back(make_int2(ta, tb));
+      // compact builder: segments of <= 15 cells and <= 16 edges
+      std::vector<int> seg(1, 0);
+      for (int s0 = 0; s0 < H.NT;) {
+        int s1 = s0;
+        while (s1 < H.NT && (s1 - s0) < NUSI_CE - 1 && edge_hi_id(s1, H.N) - edge_lo_id(s0, H.N) + 1 <= NUSI_CE) ++s1;
+        seg.push_back(s1);
+        s0 = s1;
+      }
+      std::vector<int2> ctiles;
+      for (int sb = 0; sb + 1 < (int)seg.size(); ++sb)
+        for (int sa = 0; sa <= sb; ++sa) ctiles.push_back(make_int2(sa, sb));
+      c->n_ctiles = (int)ctiles.size();
       cudaError_t e1 = upload(edge, &c->d_edgeE);
       if (e1 == cudaSuccess) e1 = upload(tiles, &c->d_tiles);
+      if (e1 == cudaSuccess) e1 = upload(seg, &c->d_seg);
+      if (e1 == cudaSuccess) e1 = upload(ctiles, &c->d_ctiles);
       if (e1 == cudaSuccess)
         e1 = cudaFuncSetAttribute(alpha_tile_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem));
       if (e1 == cudaSuccess)
@@ -381,6 +400,8 @@ static int next_events(nusi_ctx *c, cudaEvent_t **e3) {
 static int launch_xsec(nusi_ctx *c, const PointParams *d_params, int cnt, int *d_status, cudaStream_t s,
                        cudaEvent_t mid = nullptr) {
   const DeviceGrid &G = c->G;
+  const char *mode_env = getenv("NUSI_ALPHA_MODE");
+  const int mode = mode_env ? atoi(mode_env) : c->opt.elementary_mode;
   dim3 gr((G.NT + NUSI_ROWS_PER_CTA - 1) / NUSI_ROWS_PER_CTA, cnt);
   rows_kernel<<<gr, NUSI_ROWS_PER_CTA * 6, 0, s>>>(G, d_params, c->d_rows, d_status);
   if (mid) CU(cudaEventRecord(mid, s));
@@ -389,9 +410,11 @@ static int launch_xsec(nusi_ctx *c, const PointParams *d_params, int cnt, int *d
     dim3 ge((ntask + 127) / 128, cnt);
     edges_kernel<<<ge, 128, 0, s>>>(G, c->n_edges, d_params, c->d_edgeE, c->d_edges);
     dim3 gt(c->n_tiles, cnt);
-    const char *mode_env = getenv("NUSI_ALPHA_MODE");
-    const int mode = mode_env ? atoi(mode_env) : c->opt.elementary_mode;
-    if (mode == 0)
+    if (mode >= 2) {
+      dim3 gc(c->n_ctiles, cnt);
+      alpha_compact_kernel<<<gc, 256, 0, s>>>(G, c->n_edges, d_params, c->d_edges, c->d_seg, c->d_ctiles, c->d_tri, c->tstride,
+                                              d_status);
+    } else if (mode == 0)
       alpha_tile_kernel<0><<<gt, 256, sizeof(TileSmem), s>>>(G, c->n_edges, d_params, c->d_edgeE, c->d_edges, c->d_tiles,
                                                             c->d_tri, c->tstride, d_status);
     else
@@ -401,7 +424,7 @@ static int launch_xsec(nusi_ctx *c, const PointParams *d_params, int cnt, int *d
   } else {
     const long long nent = G.non_resonant ? (long long)G.NT * (G.NT - 1) / 2 : (long long)(G.NT - 1);
     dim3 ga((unsigned)((nent + 127) / 128), cnt);
-    alpha_kernel<<<ga, 128, 0, s>>>(G, d_params, c->d_tri, c->tstride, d_status);
+    alpha_kernel<<<ga, 128, 0, s>>>(G, d_params, c->d_tri, c->tstride, d_status, mode >= 2 ? 1 : 0);
   }
   c->n_launches += 2;
   CU(cudaGetLastError());

@@ -88,7 +88,7 @@ def test_source_term_device_kernel(nusi):
     ctx.close()
 
 
-@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("mode", [0, 1, 2])
 def test_cross_section_tables_vs_oracle(nusi, mode):
     z = np.load(os.path.join(GOLD, "oracle_tables.npz"))
     for (maj, nr, no) in [(1, 1, 1), (0, 1, 1), (1, 0, 1), (1, 1, 0)]:
@@ -136,7 +136,7 @@ SINGLE = ["single_m%g_g%g_maj%d_nr%d_no%d" % (m, g, maj, nr, no) for (m, g) in [
 @pytest.mark.parametrize("name", SINGLE)
 def test_flux_single_points_vs_oracle(nusi, cases, name):
     """BASELINE configs[1]: N_E = 200, Majorana / non_resonant / ordering toggled, bin by bin."""
-    for mode in (0, 1):
+    for mode in (0, 1, 2):
         _check_flux(nusi, cases, name, mode)
 
 
@@ -147,7 +147,7 @@ def test_flux_strict_1e9_where_reference_is_well_conditioned(nusi, cases, name):
     self-consistent to 1e-9."""
     z, fl, meta = cases
     c = meta[name]
-    for mode in (0, 1):
+    for mode in (0, 1, 2):
         ctx = _ctx(nusi, c, elementary_mode=mode)
         fm, ff, st = ctx.evolve(c["mphi"], c["g"], c["mntot"])
         ctx.close()
@@ -159,7 +159,7 @@ def test_flux_strict_1e9_where_reference_is_well_conditioned(nusi, cases, name):
 def test_flux_reference_examples(nusi, cases, name):
     """BASELINE configs[0] (test.cpp defaults), the reference's saved test.py case, other flavours /
     mass sums / zmax, and the class-default binning."""
-    worst, st = _check_flux(nusi, cases, name, 1)
+    worst, st = _check_flux(nusi, cases, name, 2)
     if name == "testcpp_default":
         z = cases[0]
         ctx = _ctx(nusi, cases[2][name])
@@ -229,6 +229,23 @@ def test_tiled_builder_equals_per_entry_builder_bitwise(nusi):
     t0, t1 = c0.tables(mphi, g, 0.1), c1.tables(mphi, g, 0.1)
     assert np.array_equal(t0[2], t1[2], equal_nan=True) and np.array_equal(t0[0], t1[0]) and np.array_equal(t0[1], t1[1])
     c0.close(); c1.close()
+
+
+def test_compact_builder_equals_per_entry_evaluation_bitwise(nusi):
+    """elementary_mode 2: the compact tiled kernel (16x16-vertex tiles over segments of main-grid and
+    blue-shifted cells, vertex data shared through shared memory) must produce the bits of the same
+    formulas evaluated entry by entry -- a check of the tiling / edge bookkeeping, independent of parity."""
+    mphi, g = _scan_sample(6, 9)
+    for cfg in (CFG200, dict(N_bins_E=47, lEmin=5.0, lEmax=8.0, zmax=3.0, flav=0), dict(N_bins_E=300, lEmin=12.0, lEmax=17.0, zmax=5.0, flav=2)):
+        os.environ["NUSI_NO_TILES"] = "1"
+        try:
+            c0 = nusi.Context(elementary_mode=2, **cfg)
+        finally:
+            os.environ.pop("NUSI_NO_TILES")
+        c1 = nusi.Context(elementary_mode=2, **cfg)
+        t0, t1 = c0.tables(mphi, g, 0.1), c1.tables(mphi, g, 0.1)
+        assert np.array_equal(t0[2], t1[2], equal_nan=True), cfg
+        c0.close(); c1.close()
 
 
 def test_batch_invariance_and_permutation(nusi):

@@ -21,23 +21,23 @@ print("oracle time %.1fs" % (time.time() - t0))
 ref = np.array(ref); reff = np.array(reff)
 floor = R.relerr(reff, ref).max(axis=1)  # [pts, N]
 res = {}
-for mode in (0, 1):
+for mode in (0, 1, 2):
     c = nb.Context(elementary_mode=mode, **cfg)
     fm, ff, st = c.evolve(mphi, g, 0.1)
     res[mode] = R.relerr(ff, ref).max(axis=1)
     c.close()
-print("%-22s %10s %10s %10s %10s" % ("point", "ref-floor", "mode0", "mode1", "-"))
+print("%-22s %10s %10s %10s %10s" % ("point", "ref-floor", "mode0", "mode1", "mode2"))
 for i in np.argsort(mphi):
-    print("mphi=%8.1f g=%8.2e %10.1e %10.1e %10.1e %10.1e   bins>1e-9: %3d %3d %3d %3d" % (mphi[i], g[i], floor[i].max(), res[0][i].max(), res[1][i].max(), 0.0,
-          (floor[i] > 1e-9).sum(), (res[0][i] > 1e-9).sum(), (res[1][i] > 1e-9).sum(), 0))
+    print("mphi=%8.1f g=%8.2e %10.1e %10.1e %10.1e %10.1e   bins>1e-9: %3d %3d %3d %3d" % (mphi[i], g[i], floor[i].max(), res[0][i].max(), res[1][i].max(), res[2][i].max(),
+          (floor[i] > 1e-9).sum(), (res[0][i] > 1e-9).sum(), (res[1][i] > 1e-9).sum(), (res[2][i] > 1e-9).sum()))
 tot = floor.size
-print("fraction of (point,bin) within 1e-9: ref-vs-ref %.4f  mode0 %.4f mode1 %.4f mode2 %.4f" % tuple((x <= 1e-9).sum() / tot for x in (floor, res[0], res[1], res[1])))
+print("fraction of (point,bin) within 1e-9: ref-vs-ref %.4f  mode0 %.4f mode1 %.4f mode2 %.4f" % tuple((x <= 1e-9).sum() / tot for x in (floor, res[0], res[1], res[2])))
 for k in (1, 4, 10):
     tolr = np.maximum(1e-9, k * floor)
-    print("within max(1e-9, %d x floor): mode0 %.4f mode1 %.4f mode2 %.4f" % ((k,) + tuple((res[m] <= tolr).sum() / tot for m in (0, 1, 1))))
+    print("within max(1e-9, %d x floor): mode0 %.4f mode1 %.4f mode2 %.4f" % ((k,) + tuple((res[m] <= tolr).sum() / tot for m in (0, 1, 2))))
 n = 4096
 mp = 10 ** np.random.default_rng(0).uniform(1, 4, n); gg = 10 ** np.random.default_rng(1).uniform(-5, 0, n)
-for mode in (0, 1):
+for mode in (0, 1, 2):
     c = nb.Context(elementary_mode=mode, **cfg)
     P = c.upload_points(mp, gg, 0.1)
     fm = torch.empty((n, 3, 200), dtype=torch.float64, device="cuda"); ff = torch.empty_like(fm); st = torch.zeros(n, dtype=torch.int32, device="cuda")
