@@ -5,7 +5,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libnusiprop_b200.so")
+# NUSIPROP_B200_LIB: an alternative build of the SAME library (kernel tuning experiments, tools/gpu_variants.sh)
+LIB_PATH = os.environ.get("NUSIPROP_B200_LIB") or os.path.join(_HERE, "lib", "libnusiprop_b200.so")
 
 c_double_p = C.POINTER(C.c_double)
 c_int_p = C.POINTER(C.c_int)

@@ -462,17 +462,30 @@ NUSI_HD void alpha_cell_mass_t(const PointParams &P, const PhiPhiTables *pp, int
 // Majorana non-resonant table entry from compact vertices.  Same closed forms and term order as
 // alpha_cell_mass_t<true>; the vertex sums Gs = G-- - G+- - G-+ + G++ and Hs (same signs) replace the
 // per-field sums.  l1xy: x = s'-/s'+ (m/p), y = t-/t+ (m/p).
-NUSI_HD void alpha_cell_mass_compact(const PointParams &P, const PhiPhiTables *pp, int k, double fs, const CellLogs &L,
-                                     const RowEdge &Rm, const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, double l1mm,
-                                     double l1pm, double l1mp, double l1pp, double Gs, double Hs, double &tot, int *warn) {
-  const double mphi = P.mphi, g = P.g, Ga = P.Ga;
-  const double g4 = sqr(sqr(g)), m4 = sqr(sqr(mphi));
-  const double U2 = P.U2f[k];
-  const double wgt = m4 / (2 * P.mn[k]);
+// Per-point factors of the closed forms (same expressions as in alpha_cell_mass_t, evaluated once per tile)
+struct CellConst {
+  double g4, m4, gr, c_s, c_st, lim;
+  int phiphi;
+};
+NUSI_HD void make_cell_const(const PointParams &P, CellConst &K) {
+  K.g4 = sqr(sqr(P.g));
+  K.m4 = sqr(sqr(P.mphi));
+  K.gr = P.Ga / P.mphi;
+  K.c_s = K.g4 / (8 * kPi * P.Ga * cub(P.mphi));
+  K.c_st = K.g4 / (32 * kPi * (1 + sqr(K.gr)) * K.m4);
+  K.lim = -1e-11 * sqr(sqr(P.g / P.mphi));
+  K.phiphi = P.phiphi;
+}
+// mnk, U2: mass and |U_fk|^2 of the target eigenstate
+NUSI_HD void alpha_cell_mass_compact(const CellConst &K, const PhiPhiTables *pp, double mnk, double U2, double fs,
+                                     const CellLogs &L, const RowEdge &Rm, const RowEdge &Rp, const ColEdge &Cm,
+                                     const ColEdge &Cp, double l1mm, double l1pm, double l1mp, double l1pp, double Gs,
+                                     double Hs, double &tot, int *warn) {
+  const double g4 = K.g4, m4 = K.m4, gr = K.gr;
+  const double wgt = m4 / (2 * mnk);
   const double tm = Rm.t, tp = Rp.t, sm = Cm.s, sp = Cp.s;
-  const double gr = Ga / mphi;
 
-  double a_s = g4 / (8 * kPi * Ga * cub(mphi)) * (tm - tp) * fs;
+  double a_s = K.c_s * (tm - tp) * fs;
   a_s *= U2;
   tot += wgt * a_s;
 
@@ -504,14 +517,13 @@ NUSI_HD void alpha_cell_mass_compact(const PointParams &P, const PhiPhiTables *p
   tot += wgt * a_tu;
 
   const double dS = 2 * (tm - tp) + (Rm.l1m - Rp.l1m);
-  double a_st = g4 / (32 * kPi * (1 + sqr(gr)) * m4) *
-                (Gs + 2 * (gr * Cm.args - gr * Cp.args + Cp.lam / 2. - Cm.lam / 2. + Cm.ls - Cp.ls) * dS);
+  double a_st = K.c_st * (Gs + 2 * (gr * Cm.args - gr * Cp.args + Cp.lam / 2. - Cm.lam / 2. + Cm.ls - Cp.ls) * dS);
   a_st *= U2;
   tot += wgt * a_st;
   tot += wgt * a_st;  // s-u interference = s-t for Majorana
 
   double a_pp = 0;
-  if ((sm > 4) && P.phiphi) {
+  if ((sm > 4) && K.phiphi) {
     if (sm < 1e4) {
       const double delta = sp / sm;
       a_pp = g4 / m4 * fabs(phiphi_alpha_eval(pp, sm, nlog(-sm / tm) / nlog(delta) * 1.0001, log10(delta), warn));
@@ -523,7 +535,7 @@ NUSI_HD void alpha_cell_mass_compact(const PointParams &P, const PhiPhiTables *p
   }
   tot += wgt * a_pp;
 
-  const double lim = -1e-11 * sqr(sqr(g / mphi));
+  const double lim = K.lim;
   if (warn && (a_s < 0 || a_t < lim || a_tu < lim || (a_st + a_s + a_t) < lim)) *warn |= NUSI_WARN_ALPHA;
 }
 
@@ -601,6 +613,8 @@ NUSI_HD double alpha_entry_compact(const PointParams &P, const PhiPhiTables *pp,
                                    double Epp, int *warn) {
   double tot = 0;
   const double gr = P.Ga / P.mphi;
+  CellConst K;
+  make_cell_const(P, K);
   for (int k = 0; k < 3; ++k) {
     RowEdge Rm, Rp;
     ColEdge Cm, Cp;
@@ -622,7 +636,7 @@ NUSI_HD double alpha_entry_compact(const PointParams &P, const PhiPhiTables *pp,
     L.LR2 = alpha_log_LR(sp, tm, tp);
     L.LYm = alpha_log_LY(sm, sp, tm);
     L.LYp = alpha_log_LY(sm, sp, tp);
-    alpha_cell_mass_compact(P, pp, k, alpha_s_colfactor(P, sm, sp), L, Rm, Rp, Cm, Cp, Vmm.l1, Vpm.l1, Vmp.l1, Vpp.l1,
+    alpha_cell_mass_compact(K, pp, P.mn[k], P.U2f[k], alpha_s_colfactor(P, sm, sp), L, Rm, Rp, Cm, Cp, Vmm.l1, Vpm.l1, Vmp.l1, Vpp.l1,
                             Vmm.G - Vpm.G - Vmp.G + Vpp.G, Vmm.H - Vpm.H - Vmp.H + Vpp.H, tot, warn);
   }
   return tot;
