@@ -403,7 +403,9 @@ static int launch_xsec(nusi_ctx *c, const PointParams *d_params, int cnt, int *d
   const char *mode_env = getenv("NUSI_ALPHA_MODE");
   const int mode = mode_env ? atoi(mode_env) : c->opt.elementary_mode;
   dim3 gr((G.NT + NUSI_ROWS_PER_CTA - 1) / NUSI_ROWS_PER_CTA, cnt);
-  rows_kernel<<<gr, NUSI_ROWS_PER_CTA * 6, 0, s>>>(G, d_params, c->d_rows, d_status);
+  rows_kernel<0><<<gr, NUSI_ROWS_PER_CTA * 3, 0, s>>>(G, d_params, c->d_rows, d_status);
+  rows_kernel<1><<<gr, NUSI_ROWS_PER_CTA * 3, 0, s>>>(G, d_params, c->d_rows, d_status);
+  c->n_launches += 1;
   if (mid) CU(cudaEventRecord(mid, s));
   if (c->use_tiles) {
     const int ntask = 3 * (2 * c->n_edges + G.NT);
@@ -439,24 +441,45 @@ static int launch_integrate(nusi_ctx *c, const PointParams *d_params, int cnt, d
     if (getenv("NUSI_SERIAL_INTEGRATOR")) {  // reference-shaped bin-by-bin kernel, kept for cross-checks
       if (N > 256) return fail(NUSI_E_INVALID, "serial integrator supports N_bins_E <= 256");
       integrate_kernel<1><<<cnt, ((N + 31) / 32) * 32, 0, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff);
-    } else {
-      const size_t sh = (size_t)(4 * NT + 2 * 32 + 2 * S) * sizeof(double);
-#define NUSI_WAVE(BPT, SB)                                                                                  \
+    } else if (getenv("NUSI_WAVE_INTEGRATOR")) {  // bin-owned accumulators, kept for cross-checks
+#define NUSI_WAVE(BPT, SB, NST)                                                                             \
   do {                                                                                                      \
-    CU(cudaFuncSetAttribute(integrate_wave_kernel<BPT, SB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
-    integrate_wave_kernel<BPT, SB><<<cnt, 256, sh, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff); \
+    const size_t sh = (size_t)((NST + 2) * NT + 2 * 32 + 2 * S) * sizeof(double);                           \
+    CU(cudaFuncSetAttribute(integrate_wave_kernel<BPT, SB, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
+    integrate_wave_kernel<BPT, SB, NST><<<cnt, 256, sh, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff); \
   } while (0)
       if (N <= 256 && NT <= 256 * 3)
-        NUSI_WAVE(1, 32);
+        NUSI_WAVE(1, 32, 8);
       else if (N <= 512 && NT <= 256 * 4)
-        NUSI_WAVE(2, 16);
+        NUSI_WAVE(2, 16, 8);
       else if (N <= 1024 && NT <= 256 * 6)
-        NUSI_WAVE(4, 8);
+        NUSI_WAVE(4, 8, 8);
       else if (N <= 2048 && NT <= 256 * 10)
-        NUSI_WAVE(8, 4);
+        NUSI_WAVE(8, 4, 6);
       else
         return fail(NUSI_E_INVALID, "N_bins_E > 2048 is not supported by the integrator");
 #undef NUSI_WAVE
+    } else {
+      // diagonal-owned accumulators: N <= 256 BPT bins, N + SB - 1 <= 256 DPT diagonals, NT <= 256 (BPT + 2) table rows
+#define NUSI_DIAG(BPT, SB, DPT, NST)                                                                        \
+  do {                                                                                                      \
+    const size_t sh = (size_t)((NST + 2) * NT + 2 * SB + 2 * S) * sizeof(double);                           \
+    CU(cudaFuncSetAttribute(integrate_diag_kernel<BPT, SB, DPT, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
+    integrate_diag_kernel<BPT, SB, DPT, NST><<<cnt, 256, sh, s>>>(G, d_params, c->d_rows, c->d_tri, c->tstride, d_fm, d_ff); \
+  } while (0)
+      if (N <= 225 && NT <= 256 * 3)
+        NUSI_DIAG(1, 32, 1, 8);
+      else if (N <= 256 && NT <= 256 * 3)
+        NUSI_DIAG(1, 32, 2, 8);
+      else if (N <= 512 && NT <= 256 * 4)
+        NUSI_DIAG(2, 16, 3, 8);
+      else if (N <= 1024 && NT <= 256 * 6)
+        NUSI_DIAG(4, 8, 5, 8);
+      else if (N <= 2048 && NT <= 256 * 10)
+        NUSI_DIAG(8, 4, 9, 6);
+      else
+        return fail(NUSI_E_INVALID, "N_bins_E > 2048 is not supported by the integrator");
+#undef NUSI_DIAG
     }
   } else {
     integrate_resonant_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(G, cnt, d_params, c->d_rows, c->d_tri, c->tstride,

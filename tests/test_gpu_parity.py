@@ -203,9 +203,12 @@ def _scan_sample(n, seed=0):
 
 
 def test_wave_integrator_equals_serial_integrator_bitwise(nusi):
+    """The default integrator (wavefront, diagonal-owned sums), the bin-owned wavefront kernel and the
+    reference-shaped bin-by-bin kernel produce the same bits: the accumulation order per cell is the same."""
     mphi, g = _scan_sample(48, 5)
-    for maj in (1, 0):
-        ctx = nusi.Context(majorana=maj, **CFG200)
+    for cfg in (dict(majorana=1, **CFG200), dict(majorana=0, **CFG200), dict(N_bins_E=240, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2),
+                dict(N_bins_E=97, lEmin=5.0, lEmax=8.0, zmax=2.0, flav=1)):
+        ctx = nusi.Context(**cfg)
         os.environ.pop("NUSI_SERIAL_INTEGRATOR", None)
         a = ctx.evolve(mphi, g, 0.1)
         os.environ["NUSI_SERIAL_INTEGRATOR"] = "1"
@@ -213,8 +216,24 @@ def test_wave_integrator_equals_serial_integrator_bitwise(nusi):
             b = ctx.evolve(mphi, g, 0.1)
         finally:
             os.environ.pop("NUSI_SERIAL_INTEGRATOR", None)
-        assert np.array_equal(a[0], b[0], equal_nan=True) and np.array_equal(a[1], b[1], equal_nan=True)
+        os.environ["NUSI_WAVE_INTEGRATOR"] = "1"
+        try:
+            c = ctx.evolve(mphi, g, 0.1)
+        finally:
+            os.environ.pop("NUSI_WAVE_INTEGRATOR", None)
+        assert np.array_equal(a[0], b[0], equal_nan=True) and np.array_equal(a[1], b[1], equal_nan=True), cfg
+        assert np.array_equal(a[0], c[0], equal_nan=True) and np.array_equal(a[1], c[1], equal_nan=True), cfg
         ctx.close()
+    # several bands and several bins / diagonals per thread (N_E = 500: BPT 2, SB 16, DPT 3) vs the bin-owned kernel
+    ctx = nusi.Context(N_bins_E=500, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
+    a = ctx.evolve(mphi[:3], g[:3], 0.1)
+    os.environ["NUSI_WAVE_INTEGRATOR"] = "1"
+    try:
+        c = ctx.evolve(mphi[:3], g[:3], 0.1)
+    finally:
+        os.environ.pop("NUSI_WAVE_INTEGRATOR", None)
+    assert np.array_equal(a[0], c[0], equal_nan=True)
+    ctx.close()
 
 
 def test_tiled_builder_equals_per_entry_builder_bitwise(nusi):
