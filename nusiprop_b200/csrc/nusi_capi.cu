@@ -59,6 +59,12 @@ struct nusi_ctx {
   size_t tstride = 0;
   double *d_rows = nullptr, *d_tri = nullptr, *d_work = nullptr;
   int max_chunk = 0;
+  // host-buffer path (nusi_evolve_batch): device staging of the outputs, a compute and a copy stream
+  double *d_out_fm = nullptr, *d_out_ff = nullptr;
+  int *d_out_st = nullptr;
+  int out_cap = 0;
+  cudaStream_t s_compute = nullptr, s_copy = nullptr;
+  std::vector<cudaEvent_t> ev_done;
   // timing of the last evolve call
   std::vector<cudaEvent_t> ev;  // quadruples: start, after rows_kernel, after alpha_kernel, after integrate
   int ev_used = 0;
@@ -118,6 +124,12 @@ void nusi_ctx_destroy(nusi_ctx *c) {
   double *ptrs[] = {c->d_row_lo, c->d_row_hi, c->d_dE, c->d_cz, c->d_ndz, c->d_source, c->d_Emin, c->d_Emax,
                     c->d_zsrc, c->d_rsn, c->d_pp[0], c->d_pp[1], c->d_pp[2], c->d_pp[3], c->d_pp[4],
                     c->d_rows, c->d_tri, c->d_work, c->d_edgeE, c->d_edges};
+  if (c->d_out_fm) cudaFree(c->d_out_fm);
+  if (c->d_out_ff) cudaFree(c->d_out_ff);
+  if (c->d_out_st) cudaFree(c->d_out_st);
+  if (c->s_compute) cudaStreamDestroy(c->s_compute);
+  if (c->s_copy) cudaStreamDestroy(c->s_copy);
+  for (cudaEvent_t e : c->ev_done) cudaEventDestroy(e);
   if (c->d_tiles) cudaFree(c->d_tiles);
   if (c->d_ctiles) cudaFree(c->d_ctiles);
   if (c->d_seg) cudaFree(c->d_seg);
@@ -519,11 +531,27 @@ void nusi_points_destroy(nusi_points *p) {
 }
 int nusi_points_count(const nusi_points *p) { return p ? p->n : 0; }
 
+// enqueue evolve() for points [off, off+cnt) of p (cnt <= workspace capacity); outputs indexed from the batch start
+static int evolve_range(nusi_ctx *c, const nusi_points *p, int off, int cnt, double *d_fm, double *d_ff, int *d_st,
+                        cudaStream_t s) {
+  const int N = c->H.N;
+  cudaEvent_t *e3;
+  int rc;
+  if ((rc = next_events(c, &e3))) return rc;
+  CU(cudaEventRecord(e3[0], s));
+  if ((rc = launch_xsec(c, p->d_params + off, cnt, d_st + off, s, e3[1]))) return rc;
+  CU(cudaEventRecord(e3[2], s));
+  double *fm = d_fm ? d_fm + (size_t)off * 3 * N : nullptr;
+  double *ff = d_ff ? d_ff + (size_t)off * 3 * N : nullptr;
+  if ((rc = launch_integrate(c, p->d_params + off, cnt, fm, ff, s))) return rc;
+  CU(cudaEventRecord(e3[3], s));
+  return NUSI_OK;
+}
+
 int nusi_evolve_points(nusi_ctx *c, const nusi_points *p, double *d_fm, double *d_ff, int *d_status, void *stream) {
   if (!c || !p) return NUSI_E_INVALID;
   CU(cudaSetDevice(c->opt.device));
   cudaStream_t s = (cudaStream_t)stream;
-  const int N = c->H.N;
   const int chunk = p->n < c->max_chunk ? p->n : c->max_chunk;
   int rc = ensure_workspace(c, chunk);
   if (rc) return rc;
@@ -533,46 +561,74 @@ int nusi_evolve_points(nusi_ctx *c, const nusi_points *p, double *d_fm, double *
   if (d_status) CU(cudaMemcpyAsync(d_status, p->d_status0, (size_t)p->n * sizeof(int), cudaMemcpyDeviceToDevice, s));
   for (int off = 0; off < p->n; off += chunk) {
     const int cnt = (p->n - off < chunk) ? p->n - off : chunk;
-    cudaEvent_t *e3;
-    if ((rc = next_events(c, &e3))) return rc;
-    CU(cudaEventRecord(e3[0], s));
-    if ((rc = launch_xsec(c, p->d_params + off, cnt, d_st + off, s, e3[1]))) return rc;
-    CU(cudaEventRecord(e3[2], s));
-    double *fm = d_fm ? d_fm + (size_t)off * 3 * N : nullptr;
-    double *ff = d_ff ? d_ff + (size_t)off * 3 * N : nullptr;
-    if ((rc = launch_integrate(c, p->d_params + off, cnt, fm, ff, s))) return rc;
-    CU(cudaEventRecord(e3[3], s));
+    if ((rc = evolve_range(c, p, off, cnt, d_fm, d_ff, d_st, s))) return rc;
   }
   return NUSI_OK;
 }
 
+// Host buffers in, host buffers out.  The batch runs in slices on a compute stream; the device->host copy of a
+// finished slice runs on a second stream under the next slice's kernels (effective when the caller's buffers
+// are page-locked; with pageable memory the copies are staged by the driver and still correct).
+#ifndef NUSI_E2E_SLICE
+#define NUSI_E2E_SLICE 2048
+#endif
 int nusi_evolve_batch(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
                       double *flux_mass, double *flux_fla, int *status) {
   if (!c || n <= 0 || !mphi || !g || !mntot) return NUSI_E_INVALID;
+  CU(cudaSetDevice(c->opt.device));
+  const int N = c->H.N;
+  if (!c->s_compute) {
+    CU(cudaStreamCreateWithFlags(&c->s_compute, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
+  }
+  if (n > c->out_cap) {
+    if (c->d_out_fm) cudaFree(c->d_out_fm);
+    if (c->d_out_ff) cudaFree(c->d_out_ff);
+    if (c->d_out_st) cudaFree(c->d_out_st);
+    c->d_out_fm = c->d_out_ff = nullptr;
+    c->d_out_st = nullptr;
+    c->out_cap = 0;
+    CU(cudaMalloc((void **)&c->d_out_fm, (size_t)n * 3 * N * sizeof(double)));
+    CU(cudaMalloc((void **)&c->d_out_ff, (size_t)n * 3 * N * sizeof(double)));
+    CU(cudaMalloc((void **)&c->d_out_st, (size_t)n * sizeof(int)));
+    c->out_cap = n;
+  }
   nusi_points *p = nullptr;
   int rc = nusi_points_create(c, n, mphi, g, mntot, &p);
   if (rc) return rc;
-  const size_t fb = (size_t)n * 3 * c->H.N * sizeof(double);
-  double *d_fm = nullptr, *d_ff = nullptr;
-  int *d_st = nullptr;
+  int slice = c->max_chunk < NUSI_E2E_SLICE ? c->max_chunk : NUSI_E2E_SLICE;
+  if (slice > n) slice = n;
+  rc = ensure_workspace(c, slice);
+  c->ev_used = 0;
+  c->n_launches = 0;
   cudaError_t e = cudaSuccess;
-  if (flux_mass) e = cudaMalloc((void **)&d_fm, fb);
-  if (e == cudaSuccess && flux_fla) e = cudaMalloc((void **)&d_ff, fb);
-  if (e == cudaSuccess) e = cudaMalloc((void **)&d_st, (size_t)n * sizeof(int));
-  if (e == cudaSuccess) {
-    rc = nusi_evolve_points(c, p, d_fm, d_ff, d_st, nullptr);
-    if (rc == NUSI_OK) {
-      if (flux_mass) e = cudaMemcpy(flux_mass, d_fm, fb, cudaMemcpyDeviceToHost);
-      if (e == cudaSuccess && flux_fla) e = cudaMemcpy(flux_fla, d_ff, fb, cudaMemcpyDeviceToHost);
-      if (e == cudaSuccess && status) e = cudaMemcpy(status, d_st, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost);
-      if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (rc == NUSI_OK) e = cudaMemcpyAsync(c->d_out_st, p->d_status0, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, c->s_compute);
+  size_t k = 0;
+  for (int off = 0; off < n && rc == NUSI_OK && e == cudaSuccess; off += slice, ++k) {
+    const int cnt = (n - off < slice) ? n - off : slice;
+    rc = evolve_range(c, p, off, cnt, flux_mass ? c->d_out_fm : nullptr, flux_fla ? c->d_out_ff : nullptr, c->d_out_st,
+                      c->s_compute);
+    if (rc) break;
+    if (c->ev_done.size() <= k) {
+      cudaEvent_t ev;
+      e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+      if (e != cudaSuccess) break;
+      c->ev_done.push_back(ev);
     }
+    e = cudaEventRecord(c->ev_done[k], c->s_compute);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(c->s_copy, c->ev_done[k], 0);
+    const size_t o = (size_t)off * 3 * N, b = (size_t)cnt * 3 * N * sizeof(double);
+    if (e == cudaSuccess && flux_mass) e = cudaMemcpyAsync(flux_mass + o, c->d_out_fm + o, b, cudaMemcpyDeviceToHost, c->s_copy);
+    if (e == cudaSuccess && flux_fla) e = cudaMemcpyAsync(flux_fla + o, c->d_out_ff + o, b, cudaMemcpyDeviceToHost, c->s_copy);
+    if (e == cudaSuccess && status)
+      e = cudaMemcpyAsync(status + off, c->d_out_st + off, (size_t)cnt * sizeof(int), cudaMemcpyDeviceToHost, c->s_copy);
   }
-  if (d_fm) cudaFree(d_fm);
-  if (d_ff) cudaFree(d_ff);
-  if (d_st) cudaFree(d_st);
+  cudaError_t e2 = cudaStreamSynchronize(c->s_compute);
+  cudaError_t e3 = cudaStreamSynchronize(c->s_copy);
   nusi_points_destroy(p);
   if (rc) return rc;
+  if (e == cudaSuccess) e = e2;
+  if (e == cudaSuccess) e = e3;
   if (e != cudaSuccess) return fail(NUSI_E_CUDA, std::string("evolve_batch: ") + cudaGetErrorString(e));
   return NUSI_OK;
 }
