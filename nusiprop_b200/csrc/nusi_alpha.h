@@ -28,6 +28,8 @@ struct RowEdge {
   double argn;   // carg(-(1/(1+t))): pi if 1+t > 0 else 0
   double lnD;    // ln((2+t)^2 + ga_red^2) = lam2 + 2 ln(ga_red)        (shared-logarithm builder)
   double phi;    // arg(2 + t + i ga_red) in (0, pi)                     (shared-logarithm builder)
+  double i1p;    // 1/(1+t)                                               (compact builder)
+  double i1m;    // 1/(-1+t)                                              (compact builder)
 };
 struct ColEdge {
   double s;      // s'/mphi^2 at the edge
@@ -38,6 +40,7 @@ struct ColEdge {
   double ls2;    // nlog(s/(2+s))
   double l2;     // ln(2+s)                                               (shared-logarithm builder)
   double lnN;    // ln((s-1)^2 + ga_red^2) = lam + 2 ln(ga_red)           (shared-logarithm builder)
+  double is;     // 1/s                                                   (compact builder)
 };
 struct Vertex {
   double l1;     // nlog1p(s+t)
@@ -67,6 +70,8 @@ NUSI_HD void make_row_edge(double t, double gr, bool full, RowEdge &R) {
     R.argn = (-(1 / (1 + t)) < 0) ? kPi : 0.0;
     R.lnD = R.lam2 + 2 * nlog(gr);
     R.phi = natan2(gr, 2 + t);
+    R.i1p = 1 / (1 + t);
+    R.i1m = 1 / (-1 + t);
   }
 }
 NUSI_HD void make_col_edge(double s, double gr, bool full, ColEdge &C) {
@@ -79,6 +84,7 @@ NUSI_HD void make_col_edge(double s, double gr, bool full, ColEdge &C) {
     C.ls2 = nlog(s / (2 + s));
     C.l2 = nlog(2 + s);
     C.lnN = C.lam + 2 * nlog(gr);
+    C.is = 1 / s;
   }
 }
 // everything of the Majorana closed forms that depends on one (s, t) pair
@@ -465,6 +471,7 @@ NUSI_HD void alpha_cell_mass_t(const PointParams &P, const PhiPhiTables *pp, int
 // Per-point factors of the closed forms (same expressions as in alpha_cell_mass_t, evaluated once per tile)
 struct CellConst {
   double g4, m4, gr, c_s, c_st, lim;
+  double c_t, c_tu;  // g4/(16 pi m4), g4/(32 pi m4)
   int phiphi;
 };
 NUSI_HD void make_cell_const(const PointParams &P, CellConst &K) {
@@ -474,15 +481,18 @@ NUSI_HD void make_cell_const(const PointParams &P, CellConst &K) {
   K.c_s = K.g4 / (8 * kPi * P.Ga * cub(P.mphi));
   K.c_st = K.g4 / (32 * kPi * (1 + sqr(K.gr)) * K.m4);
   K.lim = -1e-11 * sqr(sqr(P.g / P.mphi));
+  K.c_t = K.g4 / (16 * kPi * K.m4);
+  K.c_tu = K.g4 / (32 * kPi * K.m4);
   K.phiphi = P.phiphi;
 }
-// mnk, U2: mass and |U_fk|^2 of the target eigenstate
-NUSI_HD void alpha_cell_mass_compact(const CellConst &K, const PhiPhiTables *pp, double mnk, double U2, double fs,
+// wgt = mphi^4/(2 m_k), U2 = |U_fk|^2 of the target eigenstate.  RECIP: the quotients by edge quantities (1+t, -1+t, s) are
+// taken as products with the per-edge reciprocals (8 divisions per entry and mass become multiplications).
+template <bool RECIP>
+NUSI_HD void alpha_cell_mass_compact(const CellConst &K, const PhiPhiTables *pp, double wgt, double U2, double fs,
                                      const CellLogs &L, const RowEdge &Rm, const RowEdge &Rp, const ColEdge &Cm,
                                      const ColEdge &Cp, double l1mm, double l1pm, double l1mp, double l1pp, double Gs,
                                      double Hs, double &tot, int *warn) {
   const double g4 = K.g4, m4 = K.m4, gr = K.gr;
-  const double wgt = m4 / (2 * mnk);
   const double tm = Rm.t, tp = Rp.t, sm = Cm.s, sp = Cp.s;
 
   double a_s = K.c_s * (tm - tp) * fs;
@@ -494,17 +504,24 @@ NUSI_HD void alpha_cell_mass_compact(const CellConst &K, const PhiPhiTables *pp,
                     sm * sp * l1pm + sm * sp * tp * l1pm - sp * LR1 - sp * tm * LR1 - sp * tp * LR1 - sp * tm * tp * LR1 +
                     sm * sp * l1mp + sm * sp * tm * l1mp + sm * LR2 + sm * tm * LR2 + sm * tp * LR2 + sm * tm * tp * LR2 -
                     sm * sp * l1pp - sm * sp * tm * l1pp;
-  double a_t = g4 / (sm * sp * 16 * kPi * m4) *
-               (-((sm - sp) * (3 + 2 * tm * (-1 + tp) - 2 * tp) * (tm - tp)) / ((-1 + tm) * (-1 + tp)) +
-                2 * (N1) / ((1 + tm) * (1 + tp)) -
-                ((sm * sp * LYm) / sqr(1 + tm) + (((sm - sp) * (tm - tp) * (1 + tp)) / (1 + tm) - sm * sp * LYp) / sqr(1 + tp)));
+  double a_t;
+  if (RECIP)
+    a_t = K.c_t * (Cm.is * Cp.is) *
+          (-((sm - sp) * (3 + 2 * tm * (-1 + tp) - 2 * tp) * (tm - tp)) * (Rm.i1m * Rp.i1m) + 2 * (N1) * (Rm.i1p * Rp.i1p) -
+           ((sm * sp * LYm) * sqr(Rm.i1p) + (((sm - sp) * (tm - tp) * (1 + tp)) * Rm.i1p - sm * sp * LYp) * sqr(Rp.i1p)));
+  else
+    a_t = g4 / (sm * sp * 16 * kPi * m4) *
+          (-((sm - sp) * (3 + 2 * tm * (-1 + tp) - 2 * tp) * (tm - tp)) / ((-1 + tm) * (-1 + tp)) +
+           2 * (N1) / ((1 + tm) * (1 + tp)) -
+           ((sm * sp * LYm) / sqr(1 + tm) + (((sm - sp) * (tm - tp) * (1 + tp)) / (1 + tm) - sm * sp * LYp) / sqr(1 + tp)));
   if (a_t < 0) a_t = alpha_gl2d<0>(tp, tm, sm, sp) * (g4 / (16 * kPi * m4));
   a_t *= U2;
   tot += wgt * a_t;
   tot += wgt * a_t;  // u channel = t channel for Majorana
 
   const double lmp = L.lmp, lpm = L.lpm;
-  double a_tu = g4 / (32 * kPi * m4 * sm * sp * (1 + tm) * (1 + tp)) *
+  const double pre_tu = RECIP ? K.c_tu * (Cm.is * Cp.is) * (Rm.i1p * Rp.i1p) : g4 / (32 * kPi * m4 * sm * sp * (1 + tm) * (1 + tp));
+  double a_tu = pre_tu *
                 (-4 * (sm - sp) * (1 + tm) * (tm - tp) * (1 + tp) + 2 * sm * sp * tp * (lmp - l1mm + l1pm) +
                  2 * sp * (1 + tm) * (1 + tp) * (Rm.l1m - l1mm - Rp.l1m + l1mp) -
                  2 * sm * (1 + tm) * (1 + tp) * (Rm.l1m - l1pm - Rp.l1m + l1pp) + 2 * sm * sp * (-l1mm + l1pm + l1mp - l1pp) +
@@ -609,6 +626,7 @@ NUSI_HD double alpha_entry_shared(const PointParams &P, const PhiPhiTables *pp, 
 }
 
 // same, through compact vertices (what the default tiled kernel computes)
+template <bool RECIP>
 NUSI_HD double alpha_entry_compact(const PointParams &P, const PhiPhiTables *pp, double Em, double Ep, double Emp,
                                    double Epp, int *warn) {
   double tot = 0;
@@ -636,7 +654,7 @@ NUSI_HD double alpha_entry_compact(const PointParams &P, const PhiPhiTables *pp,
     L.LR2 = alpha_log_LR(sp, tm, tp);
     L.LYm = alpha_log_LY(sm, sp, tm);
     L.LYp = alpha_log_LY(sm, sp, tp);
-    alpha_cell_mass_compact(K, pp, P.mn[k], P.U2f[k], alpha_s_colfactor(P, sm, sp), L, Rm, Rp, Cm, Cp, Vmm.l1, Vpm.l1, Vmp.l1, Vpp.l1,
+    alpha_cell_mass_compact<RECIP>(K, pp, K.m4 / (2 * P.mn[k]), P.U2f[k], alpha_s_colfactor(P, sm, sp), L, Rm, Rp, Cm, Cp, Vmm.l1, Vpm.l1, Vmp.l1, Vpp.l1,
                             Vmm.G - Vpm.G - Vmp.G + Vpp.G, Vmm.H - Vpm.H - Vmp.H + Vpp.H, tot, warn);
   }
   return tot;

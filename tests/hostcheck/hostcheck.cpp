@@ -42,8 +42,10 @@ void hc_tables(double mphi, double g, double Ga, const double *mn, const double 
     if (alphaTilde) alphaTilde[i] = nusi::alphatilde_row(P, nullptr, lo[i], hi[i], warn);
     if (alpha)
       for (int m = i + 1; m < NT; ++m)
-        alpha[(size_t)i * NT + m] = (majorana && non_resonant && hc_shared_logs == 2)
-                                        ? nusi::alpha_entry_compact(P, nullptr, lo[i], hi[i], lo[m], hi[m], warn)
+        alpha[(size_t)i * NT + m] = (majorana && non_resonant && hc_shared_logs == 3)
+                                        ? nusi::alpha_entry_compact<true>(P, nullptr, lo[i], hi[i], lo[m], hi[m], warn)
+                                    : (majorana && non_resonant && hc_shared_logs == 2)
+                                        ? nusi::alpha_entry_compact<false>(P, nullptr, lo[i], hi[i], lo[m], hi[m], warn)
                                     : (majorana && non_resonant && hc_shared_logs)
                                         ? nusi::alpha_entry_shared(P, nullptr, lo[i], hi[i], lo[m], hi[m], warn)
                                         : nusi::alpha_entry(P, nullptr, lo[i], hi[i], lo[m], hi[m], warn);
