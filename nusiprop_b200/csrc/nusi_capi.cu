@@ -497,7 +497,7 @@ static int launch_integrate(nusi_ctx *c, const PointParams *d_params, int cnt, d
       // diagonal-owned accumulators: N <= 256 BPT bins, N + SB - 1 <= 256 DPT diagonals, NT <= 256 (BPT + 2) table rows
 #define NUSI_DIAG(BPT, SB, DPT, NST)                                                                        \
   do {                                                                                                      \
-    const size_t sh = (size_t)((NST + 2) * NT + 2 * SB + 2 * SB * NUSI_PRE_DOUBLES + 2 * S + N + 2) * sizeof(double); \
+    const size_t sh = (size_t)((NST + 2) * NT + 2 * SB + 2 * SB * NUSI_PRE_DOUBLES + 2 * S + 2 * N + 2) * sizeof(double); \
     CU(cudaFuncSetAttribute(integrate_diag_kernel<BPT, SB, DPT, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
     integrate_diag_kernel<BPT, SB, DPT, NST><<<cnt, 256, sh, s>>>(G, d_params, W.rows, W.tri, c->tstride, d_fm, d_ff); \
   } while (0)
