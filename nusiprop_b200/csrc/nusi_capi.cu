@@ -48,8 +48,7 @@ struct nusi_ctx {
   double *d_edgeE = nullptr;  // distinct bin-edge energies of the table cells (tiled builder)
   int2 *d_tiles = nullptr;
   int n_tiles = 0;
-  int2 *d_ctiles = nullptr;  // compact builder: (segment a, segment b) pairs and the segment boundaries
-  int *d_seg = nullptr;
+  int4 *d_ctiles = nullptr;  // compact builder: per tile the cell ranges [a0, a1) x [b0, b1) of its row / column segment
   int n_ctiles = 0;
   int n_edges = 0;
   bool use_tiles = false;
@@ -137,7 +136,6 @@ void nusi_ctx_destroy(nusi_ctx *c) {
     if (e) cudaEventDestroy(e);
   if (c->d_tiles) cudaFree(c->d_tiles);
   if (c->d_ctiles) cudaFree(c->d_ctiles);
-  if (c->d_seg) cudaFree(c->d_seg);
   for (double *p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
@@ -261,13 +259,12 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
         seg.push_back(s1);
         s0 = s1;
       }
-      std::vector<int2> ctiles;
+      std::vector<int4> ctiles;
       for (int sb = 0; sb + 1 < (int)seg.size(); ++sb)
-        for (int sa = 0; sa <= sb; ++sa) ctiles.push_back(make_int2(sa, sb));
+        for (int sa = 0; sa <= sb; ++sa) ctiles.push_back(make_int4(seg[sa], seg[sa + 1], seg[sb], seg[sb + 1]));
       c->n_ctiles = (int)ctiles.size();
       cudaError_t e1 = upload(edge, &c->d_edgeE);
       if (e1 == cudaSuccess) e1 = upload(tiles, &c->d_tiles);
-      if (e1 == cudaSuccess) e1 = upload(seg, &c->d_seg);
       if (e1 == cudaSuccess) e1 = upload(ctiles, &c->d_ctiles);
       if (e1 == cudaSuccess)
         e1 = cudaFuncSetAttribute(alpha_tile_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem));
@@ -448,7 +445,7 @@ static int launch_alpha(nusi_ctx *c, const PointParams *d_params, int cnt, int *
     dim3 gt(c->n_tiles, cnt);
     if (mode >= 2) {
       dim3 gc(c->n_ctiles, cnt);
-      alpha_compact_kernel<<<gc, 256, 0, s>>>(G, c->n_edges, d_params, W.edges, c->d_seg, c->d_ctiles, W.tri, c->tstride, d_status);
+      alpha_compact_kernel<<<gc, 256, 0, s>>>(G, c->n_edges, d_params, W.edges, c->d_ctiles, W.tri, c->tstride, d_status);
     } else if (mode == 0)
       alpha_tile_kernel<0><<<gt, 256, sizeof(TileSmem), s>>>(G, c->n_edges, d_params, c->d_edgeE, W.edges, c->d_tiles, W.tri,
                                                             c->tstride, d_status);
