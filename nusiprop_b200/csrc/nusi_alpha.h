@@ -325,6 +325,13 @@ NUSI_HD double alpha_log_LR(double s, double tm, double tp) {  // nuSIprop.hpp:1
 NUSI_HD double alpha_log_LY(double sm, double sp, double t) {  // nuSIprop.hpp:1284, "log((s-(1+s++t))/(s+(1+s-+t)))"
   return nlog((sm * (1 + sp + t)) / (sp * (1 + sm + t)));
 }
+// the same two logarithms for the compact builder: arguments are bin-to-bin ratios near 1
+NUSI_HD double alpha_log_LR_c(double s, double tm, double tp) {
+  return nlog_near1(((1 + s + tm) * (-1 + tp)) / ((-1 + tm) * (1 + s + tp)));
+}
+NUSI_HD double alpha_log_LY_c(double sm, double sp, double t) {
+  return nlog_near1((sm * (1 + sp + t)) / (sp * (1 + sm + t)));
+}
 struct CellLogs {
   double lmp, lpm;            // ln(s-/s+), ln(s+/s-)
   double LR1, LR2, LYm, LYp;  // LR at s-, s+ ; LY at t-, t+
@@ -650,10 +657,10 @@ NUSI_HD double alpha_entry_compact(const PointParams &P, const PhiPhiTables *pp,
     CellLogs L;
     L.lmp = nlog(sm / sp);
     L.lpm = nlog(sp / sm);
-    L.LR1 = alpha_log_LR(sm, tm, tp);
-    L.LR2 = alpha_log_LR(sp, tm, tp);
-    L.LYm = alpha_log_LY(sm, sp, tm);
-    L.LYp = alpha_log_LY(sm, sp, tp);
+    L.LR1 = alpha_log_LR_c(sm, tm, tp);
+    L.LR2 = alpha_log_LR_c(sp, tm, tp);
+    L.LYm = alpha_log_LY_c(sm, sp, tm);
+    L.LYp = alpha_log_LY_c(sm, sp, tp);
     alpha_cell_mass_compact<RECIP>(K, pp, K.m4 / (2 * P.mn[k]), P.U2f[k], alpha_s_colfactor(P, sm, sp), L, Rm, Rp, Cm, Cp, Vmm.l1, Vpm.l1, Vmp.l1, Vpp.l1,
                             Vmm.G - Vpm.G - Vmp.G + Vpp.G, Vmm.H - Vpm.H - Vmp.H + Vpp.H, tot, warn);
   }

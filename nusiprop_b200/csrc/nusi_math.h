@@ -120,7 +120,45 @@ NUSI_HD cplx ccub(cplx a) { return a * a * a; }
 __device__ __constant__ double nusi_bern_dev[13] = {NUSI_BERN_LIST};
 #endif
 static const double nusi_bern_host[13] = {NUSI_BERN_LIST};
+// (-1)^(n+1)/n, n = 2..17: Taylor coefficients of log(1+x) beyond the linear term
+#define NUSI_LOGC_LIST -1.0 / 2, 1.0 / 3, -1.0 / 4, 1.0 / 5, -1.0 / 6, 1.0 / 7, -1.0 / 8, 1.0 / 9, -1.0 / 10, 1.0 / 11, -1.0 / 12, \
+                       1.0 / 13, -1.0 / 14, 1.0 / 15, -1.0 / 16, 1.0 / 17
+#if defined(__CUDACC__)
+__device__ __constant__ double nusi_logc_dev[16] = {NUSI_LOGC_LIST};
+#endif
+static const double nusi_logc_host[16] = {NUSI_LOGC_LIST};
 namespace nusi {
+
+// log(r) for an argument near 1 (the bin-to-bin ratios of the compact builder: |r-1| <= 2 (delta-1), delta the
+// bin ratio).  x = r - 1 is exact for 1/2 <= r <= 2; for |x| <= 1/8 the series  x + x^2 (c2 + c3 x + ... + c17 x^15)
+// is truncated below 2^-55 |x| and the bracket carries <= 1/8 of the result's weight, so the value is within one
+// ulp of log(r) -- the accuracy of the libm logarithm it replaces -- in 18 FP64 instructions instead of ~30 plus a call.
+#if defined(__CUDA_ARCH__)
+#define NUSI_LOGC(n) nusi_logc_dev[(n)-2]
+#else
+#define NUSI_LOGC(n) nusi_logc_host[(n)-2]
+#endif
+NUSI_HD double nlog_near1(double r) {
+  const double x = r - 1.0;
+  if (!(fabs(x) <= 0.125)) return nlog(r);
+  double q = NUSI_LOGC(17);
+  q = fma(q, x, NUSI_LOGC(16));
+  q = fma(q, x, NUSI_LOGC(15));
+  q = fma(q, x, NUSI_LOGC(14));
+  q = fma(q, x, NUSI_LOGC(13));
+  q = fma(q, x, NUSI_LOGC(12));
+  q = fma(q, x, NUSI_LOGC(11));
+  q = fma(q, x, NUSI_LOGC(10));
+  q = fma(q, x, NUSI_LOGC(9));
+  q = fma(q, x, NUSI_LOGC(8));
+  q = fma(q, x, NUSI_LOGC(7));
+  q = fma(q, x, NUSI_LOGC(6));
+  q = fma(q, x, NUSI_LOGC(5));
+  q = fma(q, x, NUSI_LOGC(4));
+  q = fma(q, x, NUSI_LOGC(3));
+  q = fma(q, x, NUSI_LOGC(2));
+  return fma(x * x, q, x);
+}
 
 // Li2(y) from u = -ln(1-y), |u| <= 0.6932: (u/2pi)^2 <= 0.0122, 9 Bernoulli terms leave < 1e-19.
 // On the device the coefficients live in constant memory: a DFMA takes a constant-bank operand directly,
