@@ -19,7 +19,7 @@
 extern "C" {
 #endif
 
-#define NUSI_ABI_VERSION 1
+#define NUSI_ABI_VERSION 2
 
 /* error codes (function return values) */
 #define NUSI_OK 0
@@ -63,6 +63,14 @@ typedef struct nusi_opts {
                                 tiles, all three target masses per barrier (same closed forms; fastest).
                             Parity with the reference is at the reference's own FMA-on/off noise floor in all
                             three modes. */
+  int source_model;      /* 0 (default) = the reference's source: diffuse supernova background, Fermi-Dirac spectrum
+                                (nuSIprop.hpp:638-662; si and norm are inert there);
+                            1 = power law of the upstream code that the reference keeps commented out (:648-657):
+                                L_i(z, E) = norm_total/3 SFR(z) (E (1+z)/E0)^-si, E0 = 1e14 eV,
+                                norm_total = norm / flux_FS_E0()  (:205, :666-692) */
+  double si;             /* spectral index, source_model 1 only (default 2; si == 1 is rejected: the bin integral of
+                            :656 divides by 1 - si) */
+  double norm;           /* free-streaming flux at Earth at E0, source_model 1 only (default 1) */
 } nusi_opts;
 
 /* Fills *o with the reference's C++ constructor defaults (nuSIprop.hpp:61-65). */
@@ -99,6 +107,12 @@ int nusi_grid(int N_bins_E, double lEmin, double lEmax, double zmax, int *N_step
  * check_energy_conservation() (:339-357) compares the evolved flux with.  Host arithmetic
  * (300 pow() calls); zmax_eff is the context's effective zmax (z[N_steps_z-1]). */
 int nusi_freestream_energy(double zmax_eff, double lEmin, double lEmax, double si, double norm, double *E_FS);
+
+/* Bin-integrated power-law source of nusi_opts.source_model == 1 -- the upstream Lum() that the reference keeps as a
+ * comment (nuSIprop.hpp:648-657) with norm_total = norm / flux_FS_E0() (:205, :666-692) -- for the grids of
+ * nusi_grid(): out[(N_steps_z-1)][N_bins_E], row i at redshift z[i+1] (where the z-loop evaluates it, :283), per mass
+ * eigenstate.  Host arithmetic, no GPU (what nusi_ctx_create uploads for source_model 1; test access). */
+int nusi_powerlaw_source(int N_bins_E, double lEmin, double lEmax, double zmax, double si, double norm, double *out);
 
 /* Neutrino masses for one mntot: nuSIaux::getmL + nuSIprop.hpp:184-203.  Host arithmetic.
  * Returns NUSI_OK and mn[3], or NUSI_E_INVALID when the reference would exit(1). */

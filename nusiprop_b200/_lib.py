@@ -28,6 +28,9 @@ class NusiOpts(C.Structure):
         ("device", C.c_int),
         ("max_points_per_launch", C.c_int),
         ("elementary_mode", C.c_int),
+        ("source_model", C.c_int),
+        ("si", C.c_double),
+        ("norm", C.c_double),
     ]
 
 
@@ -46,6 +49,7 @@ SIGNATURES = {
     "nusi_ctx_source": (C.c_int, [C.c_void_p, c_double_p]),
     "nusi_grid": (C.c_int, [C.c_int, C.c_double, C.c_double, C.c_double, c_int_p, c_double_p, c_double_p, c_double_p, c_double_p]),
     "nusi_freestream_energy": (C.c_int, [C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, c_double_p]),
+    "nusi_powerlaw_source": (C.c_int, [C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, c_double_p]),
     "nusi_phiphi_tables_generate": (C.c_int, [C.c_int, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, c_double_p]),
     "nusi_masses": (C.c_int, [C.c_double, C.c_int, c_double_p]),
     "nusi_evolve_batch": (C.c_int, [C.c_void_p, C.c_int, c_double_p, c_double_p, c_double_p, c_double_p, c_double_p, c_int_p]),

@@ -31,7 +31,7 @@ class Context(object):
 
     def __init__(self, majorana=True, non_resonant=True, normal_ordering=True, N_bins_E=300, lEmin=12.0,
                  lEmax=17.0, zmax=5.0, flav=2, phiphi=False, device=0, alphatilde_phiphi_path=None,
-                 alpha_phiphi_path=None, max_points_per_launch=0, elementary_mode=None):
+                 alpha_phiphi_path=None, max_points_per_launch=0, elementary_mode=None, source_model=0, si=2.0, norm=1.0):
         self._lib = _lib.load()
         o = NusiOpts()
         check(self._lib.nusi_opts_default(C.byref(o)), "nusi_opts_default")
@@ -41,6 +41,8 @@ class Context(object):
         o.max_points_per_launch = int(max_points_per_launch)
         if elementary_mode is not None:
             o.elementary_mode = int(elementary_mode)
+        # 0: the reference's DSNB source; 1: upstream power law norm * (E/1e14 eV)^-si at Earth (nuSIprop.hpp:648-657)
+        o.source_model, o.si, o.norm = int(source_model), float(si), float(norm)
         self._paths = (
             alphatilde_phiphi_path.encode() if alphatilde_phiphi_path else None,
             alpha_phiphi_path.encode() if alpha_phiphi_path else None,
@@ -215,21 +217,32 @@ class pyprop(object):
     _ctx_cache = {}
 
     def __init__(self, mphi, g, mntot, si, norm=1, majorana=True, non_resonant=True, normal_ordering=True,
-                 N_bins_E=300, lEmin=12.0, lEmax=17.0, zmax=5.0, flav=2, phiphi=True, device=0):
+                 N_bins_E=300, lEmin=12.0, lEmax=17.0, zmax=5.0, flav=2, phiphi=True, device=0, source_model=0):
         self.mphi, self.g, self.mntot, self.si, self.norm = float(mphi), float(g), float(mntot), float(si), float(norm)
-        key = (bool(majorana), bool(non_resonant), bool(normal_ordering), int(N_bins_E), float(lEmin), float(lEmax),
-               float(zmax), int(flav), bool(phiphi), int(device))
-        ctx = pyprop._ctx_cache.get(key)
-        if ctx is None:
-            ctx = Context(majorana=majorana, non_resonant=non_resonant, normal_ordering=normal_ordering, N_bins_E=N_bins_E,
-                          lEmin=lEmin, lEmax=lEmax, zmax=zmax, flav=flav, phiphi=phiphi, device=device)
-            pyprop._ctx_cache[key] = ctx
-        self._ctx = ctx
+        # source_model (extra): 0 = the reference's DSNB source (si, norm inert, as in the reference);
+        # 1 = the upstream power law norm * (E/1e14 eV)^-si that the reference keeps commented out (hpp:648-657)
+        self._fixed = dict(majorana=bool(majorana), non_resonant=bool(non_resonant), normal_ordering=bool(normal_ordering),
+                           N_bins_E=int(N_bins_E), lEmin=float(lEmin), lEmax=float(lEmax), zmax=float(zmax), flav=int(flav),
+                           phiphi=bool(phiphi), device=int(device), source_model=int(source_model))
+        self._ctx = self._acquire()
         self.evolved = False
-        N = ctx.N_bins_E
+        N = self._ctx.N_bins_E
         self._flux = np.zeros((3, N))
         self._flux_fla = np.zeros((3, N))
         self.status = 0
+
+    def _acquire(self):
+        """Context for the fixed options (+ si, norm when they define the source); shared between objects."""
+        extra = (self.si, self.norm) if self._fixed["source_model"] == 1 else ()
+        key = tuple(sorted(self._fixed.items())) + extra
+        ctx = pyprop._ctx_cache.get(key)
+        if ctx is None:
+            kw = dict(self._fixed)
+            if extra:
+                kw.update(si=self.si, norm=self.norm)
+            ctx = Context(**kw)
+            pyprop._ctx_cache[key] = ctx
+        return ctx
 
     def set_parameters(self, mphi=None, g=None, mntot=None, si=None, norm=None):
         """Modify the physics parameters (reference nuSIprop.pyx:60-85)."""
@@ -248,6 +261,7 @@ class pyprop(object):
     def evolve(self):
         """Evolve the neutrino flux (reference nuSIprop.pyx:87-90)."""
         self.evolved = True
+        self._ctx = self._acquire()
         fm, ff, st = self._ctx.evolve(self.mphi, self.g, self.mntot)
         self.status = int(st[0])
         if self.status & 256:

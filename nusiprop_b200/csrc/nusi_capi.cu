@@ -110,6 +110,9 @@ int nusi_opts_default(nusi_opts *o) {
   o->phiphi = 0;
   o->device = 0;
   o->elementary_mode = 2;
+  o->source_model = 0;
+  o->si = 2.0;
+  o->norm = 1.0;
   return NUSI_OK;
 }
 
@@ -147,6 +150,9 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
   *out = nullptr;
   if (o->N_bins_E < 2 || !(o->lEmax > o->lEmin) || !(o->zmax > 0) || o->flav < 0 || o->flav > 2)
     return fail(NUSI_E_INVALID, "bad binning / flavour options");
+  if (o->source_model < 0 || o->source_model > 1 ||
+      (o->source_model == 1 && (!(std::fabs(1 - o->si) > 1e-12) || !std::isfinite(o->si) || !std::isfinite(o->norm))))
+    return fail(NUSI_E_INVALID, "bad source options (source_model 0 or 1; si != 1 and finite; norm finite)");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || o->device < 0 || o->device >= ndev)
     return fail(NUSI_E_NO_DEVICE, "no CUDA device with the requested ordinal");
@@ -223,7 +229,12 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
   // source term, once per context, on the device
   const int S = H.Nz - 1;
   cudaError_t e = cudaMalloc((void **)&c->d_source, (size_t)S * H.N * sizeof(double));
-  if (e == cudaSuccess) {
+  if (e == cudaSuccess && o->source_model == 1) {
+    // upstream power law (nuSIprop.hpp:648-657): host arithmetic (glibc pow), uploaded once
+    std::vector<double> src((size_t)S * H.N);
+    powerlaw_source(H.N, S, H.zsrc.data(), H.Emin.data(), H.Emax.data(), H.zmax_eff, o->si, o->norm, src.data());
+    e = cudaMemcpy(c->d_source, src.data(), src.size() * sizeof(double), cudaMemcpyHostToDevice);
+  } else if (e == cudaSuccess) {
     source_kernel<<<(S * H.N + 127) / 128, 128>>>(H.N, S, c->d_zsrc, c->d_rsn, H.lum_pref, c->d_Emin, c->d_Emax,
                                                   c->d_source);
     e = cudaGetLastError();
@@ -344,6 +355,15 @@ int nusi_grid(int N_bins_E, double lEmin, double lEmax, double zmax, int *N_step
 int nusi_freestream_energy(double zmax_eff, double lEmin, double lEmax, double si, double norm, double *E_FS) {
   if (!E_FS || !(zmax_eff > 0) || !(lEmax > lEmin)) return NUSI_E_INVALID;
   *E_FS = freestream_energy(zmax_eff, lEmin, lEmax, si, norm);
+  return NUSI_OK;
+}
+
+int nusi_powerlaw_source(int N_bins_E, double lEmin, double lEmax, double zmax, double si, double norm, double *out) {
+  if (!out || N_bins_E < 2 || !(lEmax > lEmin) || !(zmax > 0) || !(std::fabs(1 - si) > 1e-12)) return NUSI_E_INVALID;
+  HostGrid H;
+  build_grid(N_bins_E, lEmin, lEmax, zmax, true, H);
+  if (H.Nz < 2) return NUSI_E_INVALID;
+  powerlaw_source(H.N, H.Nz - 1, H.zsrc.data(), H.Emin.data(), H.Emax.data(), H.zmax_eff, si, norm, out);
   return NUSI_OK;
 }
 

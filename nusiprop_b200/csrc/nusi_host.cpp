@@ -115,6 +115,24 @@ static double gl3_panels(double z_min, double z_max, F integrand) {
   }
   return res;
 }
+// Power-law source of the upstream code (kept as a comment in the reference, nuSIprop.hpp:648-657), bin-integrated:
+//   Lum(z, Em, Ep) = norm_total/3 SFR(z) (Ep (Ep/E0 (1+z))^-si - Em (Em/E0 (1+z))^-si) / (1 - si),
+//   norm_total = norm / flux_FS_E0()  (:205), flux_FS_E0 = \int_0^zmax dz (1+z)^-si SFR/H  (:666-692).
+// out[i * N + j] for source redshift zsrc[i] (i < S; the z-loop evaluates the source at z[i+1], :283) and bin j:
+// the layout of the device source table.
+void powerlaw_source(int N, int S, const double *zsrc, const double *Emin, const double *Emax, double zmax_eff, double si,
+                     double norm, double *out) {
+  const double E0 = 1e14;
+  const double fs0 = gl3_panels(0, zmax_eff, [&](double zz) { return std::pow(1 + zz, -si) * cosmo_SFR(zz) / cosmo_H(zz); });
+  const double norm_total = norm / fs0;
+  for (int i = 0; i < S; ++i)
+    for (int j = 0; j < N; ++j) {
+      const double Ep = Emax[j], Em = Emin[j], zz = zsrc[i];
+      out[(size_t)i * N + j] = norm_total / 3.0 * cosmo_SFR(zz) *
+                               (Ep * std::pow(Ep / E0 * (1 + zz), -si) - Em * std::pow(Em / E0 * (1 + zz), -si)) / (1 - si);
+    }
+}
+
 double freestream_energy(double zmax_eff, double lEmin, double lEmax, double si, double norm) {
   const double E0 = 1e14;  // pivot energy, nuSIprop.hpp:549
   const double fs0 = gl3_panels(0, zmax_eff, [&](double z) { return std::pow(1 + z, -si) * cosmo_SFR(z) / cosmo_H(z); });

@@ -37,6 +37,8 @@ bool solve_masses(double mntot, bool normal_ordering, double mn[3]);
 double scalar_width(double mphi, double g, bool majorana);
 
 // free-streaming diagnostics: energy_FS (nuSIprop.hpp:694-744) for norm_total = norm / flux_FS_E0 (:205, :666-692)
+void powerlaw_source(int N, int S, const double *zsrc, const double *Emin, const double *Emax, double zmax_eff, double si,
+                     double norm, double *out);
 double freestream_energy(double zmax_eff, double lEmin, double lEmax, double si, double norm);
 
 // phi-phi tables: binary loader (interp.hpp:249-292) + contraction of the log10(delta) axis.

@@ -17,7 +17,10 @@
 //     NUSIPROP_B200_EXCEPTIONS is defined, in which case they throw std::runtime_error (the Cython
 //     wrapper is built that way: its pxd declares `except +`);
 //   * the getters reject bin == N_bins_E (the reference tests `j > N_bins_E` and reads past the end);
-//   * nuSIprop::evolve_scan() is new: many (mphi, g, mntot) points in one call.
+//   * nuSIprop::evolve_scan() is new: many (mphi, g, mntot) points in one call;
+//   * one extra, trailing constructor argument source_model (default 0 = the reference's DSNB source, for which si
+//     and norm are inert as in the reference; 1 = the upstream power-law source the reference keeps commented out,
+//     nuSIprop.hpp:648-657, with which check_energy_conservation() is meaningful).
 #ifndef NUSIPROP_B200_DROPIN_HPP
 #define NUSIPROP_B200_DROPIN_HPP
 
@@ -54,7 +57,8 @@ struct ctx_handle {
   ctx_handle(const ctx_handle &) = delete;
   ctx_handle &operator=(const ctx_handle &) = delete;
 };
-typedef std::tuple<bool, bool, bool, int, double, double, double, int, bool, int> ctx_key;
+// fixed options ..., device, then the source: (source_model, si, norm); si and norm are 0 for source_model 0 (inert there)
+typedef std::tuple<bool, bool, bool, int, double, double, double, int, bool, int, int, double, double> ctx_key;
 
 inline std::shared_ptr<ctx_handle> acquire_ctx(const ctx_key &key) {
   static std::map<ctx_key, std::weak_ptr<ctx_handle>> registry;
@@ -72,6 +76,11 @@ inline std::shared_ptr<ctx_handle> acquire_ctx(const ctx_key &key) {
   o.flav = std::get<7>(key);
   o.phiphi = std::get<8>(key);
   o.device = std::get<9>(key);
+  o.source_model = std::get<10>(key);
+  if (o.source_model == 1) {
+    o.si = std::get<11>(key);
+    o.norm = std::get<12>(key);
+  }
   nusi_ctx *c = nullptr;
   const int rc = nusi_ctx_create(&c, &o);
   if (rc != NUSI_OK) {
@@ -96,10 +105,10 @@ class calculate_flux {
 
   calculate_flux(double mphi_, double g_, double mntot_, double si_, double norm_ = 1, bool majorana_ = true,
                  bool non_resonant_ = true, bool normal_ordering_ = true, int N_bins_E_ = 300, double lEmin_ = 12.0,
-                 double lEmax_ = 17.0, double zmax_ = 5.0, int flav_ = 2, bool phiphi_ = false)
+                 double lEmax_ = 17.0, double zmax_ = 5.0, int flav_ = 2, bool phiphi_ = false, int source_model_ = 0)
       : mphi(mphi_), g(g_), mntot(mntot_), si(si_), norm(norm_), majorana(majorana_), non_resonant(non_resonant_),
         normal_ordering(normal_ordering_), N_bins_E(N_bins_E_), lEmin(lEmin_), lEmax(lEmax_), zmax_arg(zmax_), flav(flav_),
-        phiphi(phiphi_), device(detail::default_device()) {
+        phiphi(phiphi_), source_model(source_model_), device(detail::default_device()) {
     if (N_bins_E < 2 || !(lEmax > lEmin) || !(zmax_arg > 0) || flav < 0 || flav > 2)
       detail::fatal("nuSIprop (B200): invalid binning / flavour options");
     flux.assign(3, std::vector<double>(N_bins_E, 0.0));
@@ -111,14 +120,21 @@ class calculate_flux {
     if (nusi_grid(N_bins_E, lEmin, lEmax, zmax_arg, &N_steps_z, &zmax, Emin.data(), E_nu.data(), Emax.data()) != NUSI_OK)
       detail::fatal("nuSIprop (B200): invalid binning options");
     // the reference loads the phi-phi tables here and exits if they are missing (:166-170)
-    if (non_resonant && phiphi) ctx = detail::acquire_ctx(key());
+    if (non_resonant && phiphi) {
+      ctx_key_in_use = key();
+      ctx = detail::acquire_ctx(ctx_key_in_use);
+    }
   }
 
   /* Parameters that can be modified after an object has been created */
   double mphi, g, mntot, si, norm;
 
   void evolve() {
-    if (!ctx) ctx = detail::acquire_ctx(key());
+    // (re-)acquire: with source_model 1 the context depends on the public, modifiable si and norm
+    if (!ctx || key() != ctx_key_in_use) {
+      ctx_key_in_use = key();
+      ctx = detail::acquire_ctx(ctx_key_in_use);
+    }
     if (!ctx) return;
     std::vector<double> fm(3 * (size_t)N_bins_E), ff(3 * (size_t)N_bins_E);
     status = 0;
@@ -189,6 +205,7 @@ class calculate_flux {
   double lEmin, lEmax, zmax_arg;
   int flav;
   bool phiphi;
+  int source_model;  // extra: 0 = the reference's DSNB source, 1 = upstream power law norm (E/1e14 eV)^-si (hpp:648-657)
   int device;
   int N_steps_z = 0;
   double zmax = 0;
@@ -196,9 +213,11 @@ class calculate_flux {
   std::vector<std::vector<double>> flux, flux_fla;  // [3][N_bins_E]; copied with the object
   std::vector<double> E_nu, Emin, Emax;
   std::shared_ptr<detail::ctx_handle> ctx;  // shared, never copied
+  detail::ctx_key ctx_key_in_use;
 
   detail::ctx_key key() const {
-    return detail::ctx_key(majorana, non_resonant, normal_ordering, N_bins_E, lEmin, lEmax, zmax_arg, flav, phiphi, device);
+    return detail::ctx_key(majorana, non_resonant, normal_ordering, N_bins_E, lEmin, lEmax, zmax_arg, flav, phiphi, device,
+                           source_model, source_model == 1 ? si : 0.0, source_model == 1 ? norm : 0.0);
   }
   bool index_ok(const char *what, int i, int j) const {
     if ((i < 0) || (i >= 3)) {
@@ -225,7 +244,7 @@ inline int evolve_scan(int n, const double *mphi, const double *g, const double 
                        int N_bins_E = 300, double lEmin = 12.0, double lEmax = 17.0, double zmax = 5.0, int flav = 2,
                        bool phiphi = false) {
   std::shared_ptr<detail::ctx_handle> h = detail::acquire_ctx(detail::ctx_key(
-      majorana, non_resonant, normal_ordering, N_bins_E, lEmin, lEmax, zmax, flav, phiphi, detail::default_device()));
+      majorana, non_resonant, normal_ordering, N_bins_E, lEmin, lEmax, zmax, flav, phiphi, detail::default_device(), 0, 0.0, 0.0));
   if (!h) return NUSI_E_NO_DEVICE;
   return nusi_evolve_batch(h->c, n, mphi, g, mntot, flux_mass, flux_fla, status);
 }

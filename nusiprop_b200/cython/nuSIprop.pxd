@@ -7,7 +7,7 @@ cdef extern from "nuSIprop.hpp" namespace "nuSIprop":
                        double,
                        bint, bint, bint,
                        int, double, double,
-                       double, int, bint) except +
+                       double, int, bint, int) except +
         void evolve() except +
         double get_flux(int, int)
         double get_flux_fla(int, int)

@@ -20,9 +20,10 @@ cdef class pyprop:
 
     def __cinit__(self, double mphi, double g, double mntot, double si, double norm=1, bint majorana=True,
                   bint non_resonant=True, bint normal_ordering=True, int N_bins_E=300, double lEmin=12.0,
-                  double lEmax=17.0, double zmax=5.0, int flav=2, bint phiphi=True):
+                  double lEmax=17.0, double zmax=5.0, int flav=2, bint phiphi=True, int source_model=0):
+        # source_model (extra): 0 = the reference's DSNB source; 1 = upstream power law (reference hpp:648-657)
         self.my_object = calculate_flux(mphi, g, mntot, si, norm, majorana, non_resonant, normal_ordering,
-                                        N_bins_E, lEmin, lEmax, zmax, flav, phiphi)
+                                        N_bins_E, lEmin, lEmax, zmax, flav, phiphi, source_model)
         self.evolved = False
 
     def set_parameters(self, mphi=None, g=None, mntot=None, si=None, norm=None):

@@ -16,7 +16,7 @@ int main(int argc, char **argv) {
   const char *mode = argc > 15 ? argv[15] : "evolve";
   nuSIprop::calculate_flux evolver(atof(argv[1]), atof(argv[2]), atof(argv[3]), atof(argv[4]), atof(argv[5]), atoi(argv[6]) != 0,
                                    atoi(argv[7]) != 0, atoi(argv[8]) != 0, atoi(argv[9]), atof(argv[10]), atof(argv[11]),
-                                   atof(argv[12]), atoi(argv[13]), atoi(argv[14]) != 0);
+                                   atof(argv[12]), atoi(argv[13]), atoi(argv[14]) != 0, argc > 16 ? atoi(argv[16]) : 0);
   if (!std::strcmp(mode, "grid")) {
     for (int i = 0; i < evolver.get_N_bins_E(); ++i) std::printf("%.17g\n", evolver.get_energy(i));
     std::printf("oob %.17g %.17g\n", evolver.get_energy(-1), evolver.get_flux(3, 0));

@@ -169,3 +169,21 @@ def test_cython_pyprop_and_scan(cymod, nusi, oracle):
     with pytest.raises(RuntimeError, match="No neutrino mass spectrum"):
         q = cymod.pyprop(100.0, 1e-2, 0.01, 2.0, phiphi=False, **cfg)
         q.evolve()
+
+
+@pytest.mark.gpu
+def test_dropin_power_law_source_closes_energy_conservation(consumer, cymod):
+    """source_model = 1 (extra trailing constructor argument): the upstream power-law source (reference hpp:648-657);
+    check_energy_conservation() of the C++ class and of the Cython wrapper then measures the discretisation error."""
+    c = dict(_case(), N_bins_E=200, lEmin=12.0, lEmax=17.0)
+    args = _args(c, "conservation", si=2.5, norm=3.0)
+    args[0:2] = ["5e6", "1e-9"]  # mphi, g: free streaming
+    r = subprocess.run([consumer] + args + ["1"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    cons = float(r.stdout)
+    assert -0.03 < cons < 0
+    p = cymod.pyprop(5e6, 1e-9, 0.1, 2.5, 3.0, N_bins_E=200, lEmin=12.0, lEmax=17.0, zmax=5.0, phiphi=False, source_model=1)
+    assert p.check_energy_conservation() == pytest.approx(cons, rel=1e-12)
+    en = p.get_energies()
+    tot = p.get_flux().sum(axis=0)
+    assert np.allclose(tot / (3.0 * (en / 1e14) ** -2.5), tot[0] / (3.0 * (en[0] / 1e14) ** -2.5), rtol=1e-9)

@@ -1,0 +1,127 @@
+"""Power-law source switch: nusi_opts.source_model == 1 restores the upstream source
+that the reference keeps as a comment (nuSIprop.hpp:648-657) with norm_total = norm / flux_FS_E0() (:205).
+
+The reference cannot produce outputs for it (the code is commented out), so parity is pinned through
+  * a numpy restatement of the commented formula, built on the reference's own flux_FS_E0/get_SFR as
+    restated in nusiprop_b200/freestream.py (CPU), and
+  * properties the source was designed to have: with interactions switched off the evolved flux is
+    norm * (E/E0)^-si (the definition of norm_total), converging at first order in the bin width; it is
+    linear in norm; and check_energy_conservation() -- meaningless with the reference's DSNB source --
+    closes to the discretisation error (GPU).
+"""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+
+import nusiprop_b200 as nb
+from nusiprop_b200 import _lib, freestream as fs
+
+gpu = pytest.mark.gpu
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _grid(N, lEmin, lEmax, zmax):
+    lib = _lib.load()
+    nz, zm = C.c_int(), C.c_double()
+    Emin, Ec, Emax = np.zeros(N), np.zeros(N), np.zeros(N)
+    assert lib.nusi_grid(N, lEmin, lEmax, zmax, C.byref(nz), C.byref(zm), _dp(Emin), _dp(Ec), _dp(Emax)) == 0
+    z = np.array([math.pow(Emax[0] / Emin[0], i) - 1 for i in range(nz.value)])  # nuSIprop.hpp:126-127
+    return nz.value, zm.value, Emin, Ec, Emax, z
+
+
+@pytest.mark.parametrize("si,norm", [(2.0, 1.0), (2.5, 3.0), (3.2, 0.5), (0.5, 2.0)])
+def test_host_table_equals_restated_upstream_formula(si, norm):
+    N, lEmin, lEmax, zmax = 120, 12.0, 17.0, 5.0
+    Nz, zeff, Emin, Ec, Emax, z = _grid(N, lEmin, lEmax, zmax)
+    out = np.zeros((Nz - 1, N))
+    assert _lib.load().nusi_powerlaw_source(N, lEmin, lEmax, zmax, si, norm, _dp(out)) == 0
+    norm_total = norm / fs.flux_FS_E0(zeff, si)  # :205 with the reference's zmax = z[N_steps_z-1] (:128)
+    E0 = 1e14
+    exp = np.zeros_like(out)
+    for i in range(Nz - 1):
+        zz = z[i + 1]  # the z-loop evaluates Lum at z[i] for i = 1.. (:283)
+        for j in range(N):
+            exp[i, j] = norm_total / 3.0 * fs.get_SFR(zz) * (
+                Emax[j] * math.pow(Emax[j] / E0 * (1 + zz), -si) - Emin[j] * math.pow(Emin[j] / E0 * (1 + zz), -si)) / (1 - si)
+    assert np.all(np.isfinite(out)) and np.all(out > 0)
+    assert np.max(np.abs(out / exp - 1)) < 1e-12
+
+
+def test_host_table_rejects_bad_arguments():
+    lib = _lib.load()
+    out = np.zeros(10000)
+    assert lib.nusi_powerlaw_source(100, 12.0, 17.0, 5.0, 1.0, 1.0, _dp(out)) != 0  # 1 - si in the denominator
+    assert lib.nusi_powerlaw_source(1, 12.0, 17.0, 5.0, 2.0, 1.0, _dp(out)) != 0
+    assert lib.nusi_powerlaw_source(100, 17.0, 12.0, 5.0, 2.0, 1.0, _dp(out)) != 0
+    assert lib.nusi_powerlaw_source(100, 12.0, 17.0, 5.0, 2.0, 1.0, None) != 0
+
+
+def test_defaults_keep_the_reference_source():
+    o = _lib.NusiOpts()
+    assert _lib.load().nusi_opts_default(C.byref(o)) == 0
+    assert (o.source_model, o.si, o.norm) == (0, 2.0, 1.0)
+
+
+@gpu
+def test_context_uploads_the_host_table():
+    cfg = dict(N_bins_E=100, lEmin=12.0, lEmax=17.0, zmax=5.0)
+    c = nb.Context(source_model=1, si=2.3, norm=2.0, **cfg)
+    out = np.zeros((c.N_steps_z - 1, c.N_bins_E))
+    assert _lib.load().nusi_powerlaw_source(100, 12.0, 17.0, 5.0, 2.3, 2.0, _dp(out)) == 0
+    assert np.array_equal(c.source(), out)
+    d = nb.Context(**cfg)  # default: the DSNB source (exactly zero at these energies, E >> T = 6 MeV)
+    assert not np.array_equal(d.source(), out)
+    c.close(); d.close()
+    with pytest.raises(Exception):
+        nb.Context(source_model=1, si=1.0, **cfg)
+    with pytest.raises(Exception):
+        nb.Context(source_model=2, **cfg)
+
+
+@gpu
+@pytest.mark.parametrize("si", [2.0, 2.5, 3.0])
+def test_free_streaming_limit_is_the_power_law_at_first_order(si):
+    """g -> 0: sum_k flux_k(E) = norm (E/E0)^-si for every bin (energy and redshift grids are aligned, so even
+    the top bins are complete); the implicit first-order scheme converges like 1/N_bins_E."""
+    norm, err = 3.0, {}
+    for N in (100, 200, 400):
+        c = nb.Context(N_bins_E=N, lEmin=12.0, lEmax=17.0, zmax=5.0, source_model=1, si=si, norm=norm)
+        fm, ff, st = c.evolve(np.array([1e7]), np.array([1e-9]), np.array([0.1]))
+        assert st[0] == 0
+        Ec = c.energies()[1]
+        ratio = fm[0].sum(axis=0) / (norm * (Ec / 1e14) ** (-si))
+        assert ratio.max() - ratio.min() < 1e-9  # same factor in every bin: a pure discretisation constant
+        err[N] = 1 - ratio.mean()
+        # flavour projection of an equal-mass-state flux is the same flux in every flavour (unitarity)
+        assert np.allclose(ff[0], fm[0].sum(axis=0) / 3, rtol=1e-12)
+        c.close()
+    assert 0 < err[400] < err[200] < err[100] < 0.06
+    assert 1.7 < err[100] / err[200] < 2.3 and 1.7 < err[200] / err[400] < 2.3
+
+
+@gpu
+def test_linear_in_norm_and_energy_conservation():
+    cfg = dict(N_bins_E=200, lEmin=12.0, lEmax=17.0, zmax=5.0, phiphi=False, source_model=1)
+    a = nb.pyprop(5e6, 0.05, 0.1, 2.5, 1.0, **cfg)
+    b = nb.pyprop(5e6, 0.05, 0.1, 2.5, 4.0, **cfg)
+    a.evolve(); b.evolve()
+    fa, fb = a.get_flux(), b.get_flux()
+    nz = fa > 0
+    assert nz.sum() > 500 and np.max(np.abs(fb[nz] / fa[nz] / 4.0 - 1)) < 1e-12  # the transport equation is linear
+    # free streaming: only the discretisation error remains; interacting: scattering moves energy, total is conserved
+    # up to what leaves through the lower edge of the grid
+    free = nb.pyprop(5e6, 1e-9, 0.1, 2.5, 1.0, **cfg).check_energy_conservation()
+    inter = a.check_energy_conservation()
+    assert -0.03 < free < 0 and -0.06 < inter < 0.01
+    # the reference's own combination (DSNB source against the power-law free-streaming energy) is not a conservation test
+    ref_like = nb.pyprop(5e6, 0.05, 0.1, 2.5, 1.0, N_bins_E=200, lEmin=12.0, lEmax=17.0, zmax=5.0, phiphi=False)
+    assert abs(ref_like.check_energy_conservation() + 1) < 1e-6
+    # changing si / norm after construction takes effect (they are public, modifiable members in the reference)
+    a.set_parameters(norm=4.0)
+    a.evolve()
+    assert np.array_equal(a.get_flux(), fb)
