@@ -518,18 +518,36 @@ static int launch_integrate(nusi_ctx *c, const PointParams *d_params, int cnt, d
     CU(cudaFuncSetAttribute(integrate_diag_kernel<BPT, SB, DPT, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
     integrate_diag_kernel<BPT, SB, DPT, NST><<<cnt, 256, sh, s>>>(G, d_params, W.rows, W.tri, c->tstride, d_fm, d_ff); \
   } while (0)
+      // More threads per point for finer binning = fewer bins and diagonals per thread, so wide bands still fit the
+      // registers and the table is streamed fewer times (bands x waves is what a latency-bound point pays for).
+      // NUSI_FINE_VARIANT=0 selects the 256-thread configurations throughout (kept for comparison).
+#define NUSI_DIAG_T(BPT, SB, DPT, NST, NTHR)                                                                \
+  do {                                                                                                      \
+    const size_t sh = (size_t)((NST + 2) * NT + 2 * SB + 2 * SB * NUSI_PRE_DOUBLES + 2 * S + 2 * N + 2) * sizeof(double); \
+    CU(cudaFuncSetAttribute(integrate_diag_kernel<BPT, SB, DPT, NST, NTHR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
+    integrate_diag_kernel<BPT, SB, DPT, NST, NTHR><<<cnt, NTHR, sh, s>>>(G, d_params, W.rows, W.tri, c->tstride, d_fm, d_ff); \
+  } while (0)
+      const char *fv = getenv("NUSI_FINE_VARIANT");
+      const bool wide = !(fv && atoi(fv) == 0);
       if (N <= 225 && NT <= 256 * 3)
         NUSI_DIAG(1, 32, 1, 8);
       else if (N <= 256 && NT <= 256 * 3)
         NUSI_DIAG(1, 32, 2, 8);
+      else if (wide && N + 32 - 1 <= 512 && NT <= 512 * 3)
+        NUSI_DIAG_T(1, 32, 1, 8, 512);
       else if (N <= 512 && NT <= 256 * 4)
         NUSI_DIAG(2, 16, 3, 8);
+      else if (wide && N <= 1024 && NT <= 512 * 4)
+        NUSI_DIAG_T(2, 16, 3, 8, 512);
       else if (N <= 1024 && NT <= 256 * 6)
         NUSI_DIAG(4, 8, 5, 8);
+      else if (wide && N + 8 - 1 <= 512 * 4 && NT <= 512 * 6)
+        NUSI_DIAG_T(4, 8, 4, 6, 512);
       else if (N <= 2048 && NT <= 256 * 10)
         NUSI_DIAG(8, 4, 9, 6);
       else
         return fail(NUSI_E_INVALID, "N_bins_E > 2048 is not supported by the integrator");
+#undef NUSI_DIAG_T
 #undef NUSI_DIAG
     }
   } else {

@@ -242,6 +242,30 @@ def test_wave_integrator_equals_serial_integrator_bitwise(nusi):
     ctx.close()
 
 
+@pytest.mark.parametrize("N_E", [300, 900, 1100])
+def test_wide_integrator_configurations_equal_wave_kernel(nusi, N_E):
+    """Finer binning runs 512 threads per point (N_E = 300, the class default: BPT 1, SB 32; 900: BPT 2, SB 16, DPT 3;
+    1100: BPT 4, SB 8, DPT 4, as N_E = 2000).  Same accumulation order as the bin-owned wave kernel and as the
+    256-thread configurations (NUSI_FINE_VARIANT=0)."""
+    mphi, g = _scan_sample(3, 11)
+    ctx = nusi.Context(N_bins_E=N_E, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
+    a = ctx.evolve(mphi, g, 0.1)
+    try:
+        os.environ["NUSI_WAVE_INTEGRATOR"] = "1"
+        c = ctx.evolve(mphi, g, 0.1)
+        os.environ.pop("NUSI_WAVE_INTEGRATOR", None)
+        os.environ["NUSI_FINE_VARIANT"] = "0"
+        b = ctx.evolve(mphi, g, 0.1)
+    finally:
+        os.environ.pop("NUSI_WAVE_INTEGRATOR", None)
+        os.environ.pop("NUSI_FINE_VARIANT", None)
+    ok = ~np.isnan(c[0])
+    assert ok.any() and np.array_equal(np.isnan(a[0]), np.isnan(c[0]))
+    assert np.array_equal(a[0], b[0], equal_nan=True) and np.array_equal(a[1], b[1], equal_nan=True)
+    assert np.all(np.abs(a[0][ok] - c[0][ok]) <= 1e-14 * np.abs(c[0][ok]) + 1e-300)
+    ctx.close()
+
+
 def test_tiled_builder_equals_per_entry_builder_bitwise(nusi):
     """elementary_mode 0: the tiled kernel (shared vertices) must produce the per-entry kernel's bits."""
     mphi, g = _scan_sample(6, 7)
