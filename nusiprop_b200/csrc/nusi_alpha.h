@@ -249,6 +249,71 @@ NUSI_HD void make_vertex_compact(const RowEdge &R, const ColEdge &C, double gr, 
         l1 * (C.lam - R.lam2 - 2 * (C.ls - R.lfabs));
 }
 
+// ---- compact vertex, split for parameter scans ------------------------------------------------
+// Points of a scan that share (mphi, m_nu) differ only in the coupling g, which enters a vertex through
+// ga_red alone (the complex dilogarithm and the arg / Breit-Wigner-logarithm terms of G).  The two functions
+// below are make_vertex_compact() cut at that line: the SAME operations on the SAME operands in the same
+// order, so their composition equals make_vertex_compact() bit for bit (tests/test_host_math.py asserts it on
+// the host build, tests/test_gpu_parity.py on the device).
+struct VertexS {
+  double l1, H, zr_re;  // everything of a vertex that does not depend on g
+};
+NUSI_HD void make_vertex_compact_shared(const RowEdge &R, const ColEdge &C, VertexS &V) {
+  const double s = C.s, t = R.t;
+  const double one_st = 1 + s + t, d = 1 + t;
+  const double l1 = nlog1p(s + t);
+  V.l1 = l1;
+  double K;
+  if (t < -1) {
+    const double lnx = l1 - C.ls, ln1mx = R.labs - C.ls;  // x = (1+s+t)/s
+    K = (one_st <= 0.5 * s) ? li2_from_u(-ln1mx) : kZeta2 - lnx * ln1mx - li2_from_u(-lnx);
+  } else {
+    const double lnx = C.ls - l1, ln1mx = R.labs - l1;  // x = s/(1+s+t)
+    const double dF = (s <= 0.5 * one_st) ? li2_from_u(-ln1mx) : kZeta2 - lnx * ln1mx - li2_from_u(-lnx);
+    K = -dF - 0.5 * sqr(l1 - C.ls);
+  }
+  {
+    const double lnx = l1 - C.l2, ln1mx = R.l1m - C.l2;  // x = (1+s+t)/(2+s)
+    const double d2 = (one_st <= 0.5 * (2 + s)) ? li2_from_u(-ln1mx) : kZeta2 - lnx * ln1mx - li2_from_u(-lnx);
+    V.H = d2 - K;
+  }
+  const double lnzr = l1 - R.labs;
+  if (d > 0) {
+    V.zr_re = (s > d) ? 2.0 * kZeta2 - 0.5 * lnzr * lnzr - li2_from_u(l1 - C.ls)
+                      : kZeta2 - lnzr * (C.ls - R.labs) - li2_from_u(-lnzr);
+  } else {
+    V.zr_re = (s > -2.0 * d) ? -kZeta2 - 0.5 * lnzr * lnzr - li2_from_u(l1 - C.ls) : li2_from_u(R.labs - C.ls);
+  }
+}
+// the g-dependent rest: G of make_vertex_compact() from the shared l1 and zr_re
+NUSI_HD double make_vertex_compact_G(const RowEdge &R, const ColEdge &C, double gr, double l1, double zr_re) {
+  const double s = C.s, t = R.t;
+  const double one_st = 1 + s + t, d = 1 + t;
+  const double lnzr = l1 - R.labs;
+  const double zr_im = (d > 0) ? -kPi * lnzr : 0.0;
+  const double D = sqr(2 + t) + sqr(gr);
+  const bool inv = sqr(one_st) > D;
+  const bool refl = inv ? ((2 + t) > 0.5 * one_st) : (one_st * (2 + t) > 0.5 * D);
+  const double lnr = l1 - 0.5 * R.lnD;
+  const double lnw = inv ? -lnr : lnr, argw = inv ? -R.phi : R.phi;
+  const double lnomw = inv ? 0.5 * C.lnN - l1 : 0.5 * (C.lnN - R.lnD);
+  const double argomw = inv ? C.args : C.args - kPi + R.phi;
+  cplx res;
+  if (refl) {
+    const cplx tt = li2_from_u_cplx(mk(-lnw, -argw));
+    res = mk(-tt.re + kZeta2 - lnw * lnomw + argw * argomw, -tt.im - argw * lnomw - argomw * lnw);
+  } else {
+    res = li2_from_u_cplx(mk(-lnomw, -argomw));
+  }
+  if (inv) {
+    const double lim = R.phi - kPi;
+    res = mk(-res.re - 0.5 * (lnr * lnr - lim * lim) - kZeta2, -res.im - lnr * lim);
+  }
+  const double ca = C.args + R.phi - kPi;
+  return 2 * gr * (zr_im - res.im) - 2 * (zr_re - res.re) + 2 * gr * (R.argn - ca) * l1 +
+         l1 * (C.lam - R.lam2 - 2 * (C.ls - R.lfabs));
+}
+
 // 3x3 Gauss-Legendre fallback on  y in [t+, t-], x in [s-, s+]  (nuSIprop.hpp:1288-1303 etc.)
 // KIND 0: t and u propagators (Majorana t), 1: single propagator (Dirac t, u), 2: t-u interference
 template <int KIND>
@@ -563,6 +628,69 @@ NUSI_HD void alpha_cell_mass_compact(const CellConst &K, const PhiPhiTables *pp,
   if (warn && (a_s < 0 || a_t < lim || a_tu < lim || (a_st + a_s + a_t) < lim)) *warn |= NUSI_WARN_ALPHA;
 }
 
+// ---- compact cell, split for parameter scans --------------------------------------------------
+// alpha_cell_mass_compact<true>() cut the same way: the brackets of the t channel (X) and of the t-u
+// interference (Y) do not contain g; the prefactors, the s channel and the s-t interference do.  Same
+// operations, operands and order as alpha_cell_mass_compact<true> (phiphi off), so X/Y computed once per
+// (mphi, m_nu) group and combined per g reproduce it bit for bit.
+struct CellShared {
+  double X, Y;
+};
+NUSI_HD void alpha_cell_shared(const CellLogs &L, const RowEdge &Rm, const RowEdge &Rp, const ColEdge &Cm,
+                               const ColEdge &Cp, double l1mm, double l1pm, double l1mp, double l1pp, double Hs,
+                               CellShared &O) {
+  const double tm = Rm.t, tp = Rp.t, sm = Cm.s, sp = Cp.s;
+  const double LR1 = L.LR1, LR2 = L.LR2, LYm = L.LYm, LYp = L.LYp;
+  const double N1 = sm * sp * (-tm + tp) * Cm.ls + sm * sp * (tm - tp) * Cp.ls - sm * sp * l1mm - sm * sp * tp * l1mm +
+                    sm * sp * l1pm + sm * sp * tp * l1pm - sp * LR1 - sp * tm * LR1 - sp * tp * LR1 - sp * tm * tp * LR1 +
+                    sm * sp * l1mp + sm * sp * tm * l1mp + sm * LR2 + sm * tm * LR2 + sm * tp * LR2 + sm * tm * tp * LR2 -
+                    sm * sp * l1pp - sm * sp * tm * l1pp;
+  O.X = (-((sm - sp) * (3 + 2 * tm * (-1 + tp) - 2 * tp) * (tm - tp)) * (Rm.i1m * Rp.i1m) + 2 * (N1) * (Rm.i1p * Rp.i1p) -
+         ((sm * sp * LYm) * sqr(Rm.i1p) + (((sm - sp) * (tm - tp) * (1 + tp)) * Rm.i1p - sm * sp * LYp) * sqr(Rp.i1p)));
+  const double lmp = L.lmp, lpm = L.lpm;
+  O.Y = (-4 * (sm - sp) * (1 + tm) * (tm - tp) * (1 + tp) + 2 * sm * sp * tp * (lmp - l1mm + l1pm) +
+         2 * sp * (1 + tm) * (1 + tp) * (Rm.l1m - l1mm - Rp.l1m + l1mp) -
+         2 * sm * (1 + tm) * (1 + tp) * (Rm.l1m - l1pm - Rp.l1m + l1pp) + 2 * sm * sp * (-l1mm + l1pm + l1mp - l1pp) +
+         sm * sp * (1 + tm) * (1 + tp) *
+             (Cm.l2s * (Cp.ls + l1mp) - Cp.l2s * (Cm.ls + l1pp) + Rp.l1m * (lmp - l1mp + l1pp)) +
+         sm * sp * (1 + tm) * (1 + tp) *
+             ((Cp.ls + l1mm) * (Cm.ls2 + Rm.l1m - Rm.labs) + (Cm.ls + l1pm) * (Cp.l2s - Rm.l1m + Rm.labs)) +
+         sm * sp * (lpm + l1mp - l1pp) * (2 * tm + (1 + tm) * (1 + tp) * Rp.labs) + sm * sp * (1 + tm) * (1 + tp) * Hs);
+}
+NUSI_HD void alpha_cell_combine(const CellConst &K, double wgt, double U2, double fs, const RowEdge &Rm,
+                                const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, double X, double Y, double Gs,
+                                double &tot, int *warn) {
+  const double g4 = K.g4, m4 = K.m4, gr = K.gr;
+  const double tm = Rm.t, tp = Rp.t, sm = Cm.s, sp = Cp.s;
+
+  double a_s = K.c_s * (tm - tp) * fs;
+  a_s *= U2;
+  tot += wgt * a_s;
+
+  double a_t = K.c_t * (Cm.is * Cp.is) * X;
+  if (a_t < 0) a_t = alpha_gl2d<0>(tp, tm, sm, sp) * (g4 / (16 * kPi * m4));
+  a_t *= U2;
+  tot += wgt * a_t;
+  tot += wgt * a_t;  // u channel = t channel for Majorana
+
+  const double pre_tu = K.c_tu * (Cm.is * Cp.is) * (Rm.i1p * Rp.i1p);
+  double a_tu = pre_tu * Y;
+  a_tu *= U2;
+  tot += wgt * a_tu;
+
+  const double dS = 2 * (tm - tp) + (Rm.l1m - Rp.l1m);
+  double a_st = K.c_st * (Gs + 2 * (gr * Cm.args - gr * Cp.args + Cp.lam / 2. - Cm.lam / 2. + Cm.ls - Cp.ls) * dS);
+  a_st *= U2;
+  tot += wgt * a_st;
+  tot += wgt * a_st;  // s-u interference = s-t for Majorana
+
+  const double a_pp = 0;  // grouped builder runs with phiphi off only
+  tot += wgt * a_pp;
+
+  const double lim = K.lim;
+  if (warn && (a_s < 0 || a_t < lim || a_tu < lim || (a_st + a_s + a_t) < lim)) *warn |= NUSI_WARN_ALPHA;
+}
+
 NUSI_HD void alpha_cell_mass(const PointParams &P, const PhiPhiTables *pp, int k, double fs, const RowEdge &Rm,
                              const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, const Vertex &Vmm,
                              const Vertex &Vpm, const Vertex &Vmp, const Vertex &Vpp, double &tot, int *warn) {
@@ -663,6 +791,43 @@ NUSI_HD double alpha_entry_compact(const PointParams &P, const PhiPhiTables *pp,
     L.LYp = alpha_log_LY_c(sm, sp, tp);
     alpha_cell_mass_compact<RECIP>(K, pp, K.m4 / (2 * P.mn[k]), P.U2f[k], alpha_s_colfactor(P, sm, sp), L, Rm, Rp, Cm, Cp, Vmm.l1, Vpm.l1, Vmp.l1, Vpp.l1,
                             Vmm.G - Vpm.G - Vmp.G + Vpp.G, Vmm.H - Vpm.H - Vmp.H + Vpp.H, tot, warn);
+  }
+  return tot;
+}
+
+// same entry through the split (shared / per-g) vertex and cell functions: what the grouped scan builder computes
+NUSI_HD double alpha_entry_grouped(const PointParams &P, double Em, double Ep, double Emp, double Epp, int *warn) {
+  double tot = 0;
+  const double gr = P.Ga / P.mphi;
+  CellConst K;
+  make_cell_const(P, K);
+  for (int k = 0; k < 3; ++k) {
+    RowEdge Rm, Rp;
+    ColEdge Cm, Cp;
+    VertexS Vmm, Vpm, Vmp, Vpp;
+    const double tm = t_of(P.mn[k], Em, P.mphi), tp = t_of(P.mn[k], Ep, P.mphi);
+    const double sm = s_of(P.mn[k], Emp, P.mphi), sp = s_of(P.mn[k], Epp, P.mphi);
+    make_row_edge(tm, gr, true, Rm);
+    make_row_edge(tp, gr, true, Rp);
+    make_col_edge(sm, gr, true, Cm);
+    make_col_edge(sp, gr, true, Cp);
+    make_vertex_compact_shared(Rm, Cm, Vmm);
+    make_vertex_compact_shared(Rm, Cp, Vpm);
+    make_vertex_compact_shared(Rp, Cm, Vmp);
+    make_vertex_compact_shared(Rp, Cp, Vpp);
+    CellLogs L;
+    L.lmp = nlog(sm / sp);
+    L.lpm = nlog(sp / sm);
+    L.LR1 = alpha_log_LR_c(sm, tm, tp);
+    L.LR2 = alpha_log_LR_c(sp, tm, tp);
+    L.LYm = alpha_log_LY_c(sm, sp, tm);
+    L.LYp = alpha_log_LY_c(sm, sp, tp);
+    CellShared O;
+    alpha_cell_shared(L, Rm, Rp, Cm, Cp, Vmm.l1, Vpm.l1, Vmp.l1, Vpp.l1, Vmm.H - Vpm.H - Vmp.H + Vpp.H, O);
+    const double Gmm = make_vertex_compact_G(Rm, Cm, gr, Vmm.l1, Vmm.zr_re), Gpm = make_vertex_compact_G(Rm, Cp, gr, Vpm.l1, Vpm.zr_re);
+    const double Gmp = make_vertex_compact_G(Rp, Cm, gr, Vmp.l1, Vmp.zr_re), Gpp = make_vertex_compact_G(Rp, Cp, gr, Vpp.l1, Vpp.zr_re);
+    alpha_cell_combine(K, K.m4 / (2 * P.mn[k]), P.U2f[k], alpha_s_colfactor(P, sm, sp), Rm, Rp, Cm, Cp, O.X, O.Y,
+                       Gmm - Gpm - Gmp + Gpp, tot, warn);
   }
   return tot;
 }

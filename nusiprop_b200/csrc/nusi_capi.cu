@@ -37,6 +37,11 @@ static cudaError_t upload(const std::vector<T> &h, T **d) {
   return cudaMemcpy(*d, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
 }
 
+#ifndef NUSI_SLICE
+#define NUSI_SLICE 2048  // points per slice of the evolve pipeline (run_pipeline)
+#endif
+#define NUSI_GROUP_CAP 256  // most points of one scan-builder group
+
 struct nusi_ctx {
   nusi_opts opt;
   HostGrid H;
@@ -48,6 +53,7 @@ struct nusi_ctx {
   double *d_edgeE = nullptr;  // distinct bin-edge energies of the table cells (tiled builder)
   int2 *d_tiles = nullptr;
   int n_tiles = 0;
+  int2 *d_unit_groups = nullptr;  // (0, L) for L = 0..NUSI_GROUP_CAP: one-group launches of the scan builder
   int4 *d_ctiles = nullptr;  // compact builder: per tile the cell ranges [a0, a1) x [b0, b1) of its row / column segment
   int n_ctiles = 0;
   int n_edges = 0;
@@ -78,6 +84,12 @@ struct nusi_points {
   PointParams *d_params = nullptr;
   int *d_status0 = nullptr;  // host-side status (NO_MASS) pre-uploaded, OR'ed into the outputs
   std::vector<int> h_status0;
+  // scan builder (elementary_mode 3): runs of consecutive points with identical (mphi, m_nu), cut at slice boundaries
+  // and at NUSI_GROUP_MAX points; (first point relative to its slice, length)
+  int2 *d_groups = nullptr;
+  std::vector<int2> h_groups;  // host copy with ABSOLUTE first point (nusi_tables_batch)
+  std::vector<int> slice_g0;  // slice k owns groups [slice_g0[k], slice_g0[k+1])
+  int SL = 0;                 // the slice length the groups were cut for
 };
 
 extern "C" {
@@ -109,7 +121,7 @@ int nusi_opts_default(nusi_opts *o) {
   o->flav = 2;
   o->phiphi = 0;
   o->device = 0;
-  o->elementary_mode = 2;
+  o->elementary_mode = 3;
   o->source_model = 0;
   o->si = 2.0;
   o->norm = 1.0;
@@ -139,6 +151,7 @@ void nusi_ctx_destroy(nusi_ctx *c) {
     if (e) cudaEventDestroy(e);
   if (c->d_tiles) cudaFree(c->d_tiles);
   if (c->d_ctiles) cudaFree(c->d_ctiles);
+  if (c->d_unit_groups) cudaFree(c->d_unit_groups);
   for (double *p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
@@ -277,6 +290,9 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
       cudaError_t e1 = upload(edge, &c->d_edgeE);
       if (e1 == cudaSuccess) e1 = upload(tiles, &c->d_tiles);
       if (e1 == cudaSuccess) e1 = upload(ctiles, &c->d_ctiles);
+      std::vector<int2> unit;
+      for (int L = 0; L <= NUSI_GROUP_CAP; ++L) unit.push_back(make_int2(0, L));
+      if (e1 == cudaSuccess) e1 = upload(unit, &c->d_unit_groups);
       if (e1 == cudaSuccess)
         e1 = cudaFuncSetAttribute(alpha_tile_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem));
       if (e1 == cudaSuccess)
@@ -454,7 +470,8 @@ static int launch_rows(nusi_ctx *c, const PointParams *d_params, int cnt, int *d
 }
 
 // alpha table of `cnt` points
-static int launch_alpha(nusi_ctx *c, const PointParams *d_params, int cnt, int *d_status, const WorkSlot &W, cudaStream_t s) {
+static int launch_alpha(nusi_ctx *c, const PointParams *d_params, int cnt, int *d_status, const WorkSlot &W, cudaStream_t s,
+                        const int2 *d_groups = nullptr, int ngroups = 0) {
   const DeviceGrid &G = c->G;
   const char *mode_env = getenv("NUSI_ALPHA_MODE");
   const int mode = mode_env ? atoi(mode_env) : c->opt.elementary_mode;
@@ -463,7 +480,11 @@ static int launch_alpha(nusi_ctx *c, const PointParams *d_params, int cnt, int *
     dim3 ge((ntask + 127) / 128, cnt);
     edges_kernel<<<ge, 128, 0, s>>>(G, c->n_edges, d_params, c->d_edgeE, W.edges);
     dim3 gt(c->n_tiles, cnt);
-    if (mode >= 2) {
+    if (mode >= 3 && d_groups && ngroups > 0 && !G.phiphi) {
+      // scan builder: one CTA per (tile, group of points with the same mphi and neutrino masses)
+      dim3 gg(c->n_ctiles, ngroups);
+      alpha_group_kernel<<<gg, 256, 0, s>>>(G, c->n_edges, d_params, W.edges, c->d_ctiles, d_groups, W.tri, c->tstride, d_status);
+    } else if (mode >= 2) {
       dim3 gc(c->n_ctiles, cnt);
       alpha_compact_kernel<<<gc, 256, 0, s>>>(G, c->n_edges, d_params, W.edges, c->d_ctiles, W.tri, c->tstride, d_status);
     } else if (mode == 0)
@@ -568,8 +589,30 @@ int nusi_points_create(nusi_ctx *c, int n, const double *mphi, const double *g, 
   p->n = n;
   p->device = c->opt.device;
   prepare_points(c, n, mphi, g, mntot, pp, p->h_status0);
+  std::vector<int2> groups;
+  {
+    const char *gm = getenv("NUSI_GROUP_MAX");
+    const int gmax = gm ? (atoi(gm) > 0 ? (atoi(gm) < NUSI_GROUP_CAP ? atoi(gm) : NUSI_GROUP_CAP) : 1) : 32;
+    p->SL = c->max_chunk < NUSI_SLICE ? c->max_chunk : NUSI_SLICE;
+    for (int off = 0; off < n; off += p->SL) {
+      p->slice_g0.push_back((int)groups.size());
+      const int end = (n - off < p->SL) ? n : off + p->SL;
+      for (int i = off; i < end;) {
+        int j = i + 1;
+        while (j < end && j - i < gmax && std::memcmp(&pp[j].mphi, &pp[i].mphi, sizeof(double)) == 0 &&
+               std::memcmp(pp[j].mn, pp[i].mn, sizeof(pp[i].mn)) == 0)
+          ++j;
+        groups.push_back(make_int2(i - off, j - i));
+        p->h_groups.push_back(make_int2(i, j - i));
+        i = j;
+      }
+    }
+    p->slice_g0.push_back((int)groups.size());
+  }
   cudaError_t e = cudaMalloc((void **)&p->d_params, (size_t)n * sizeof(PointParams));
   if (e == cudaSuccess) e = cudaMalloc((void **)&p->d_status0, (size_t)n * sizeof(int));
+  if (e == cudaSuccess) e = cudaMalloc((void **)&p->d_groups, groups.size() * sizeof(int2));
+  if (e == cudaSuccess) e = cudaMemcpy(p->d_groups, groups.data(), groups.size() * sizeof(int2), cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(p->d_params, pp.data(), (size_t)n * sizeof(PointParams), cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpy(p->d_status0, p->h_status0.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
@@ -584,6 +627,7 @@ void nusi_points_destroy(nusi_points *p) {
   cudaSetDevice(p->device);
   if (p->d_params) cudaFree(p->d_params);
   if (p->d_status0) cudaFree(p->d_status0);
+  if (p->d_groups) cudaFree(p->d_groups);
   delete p;
 }
 int nusi_points_count(const nusi_points *p) { return p ? p->n : 0; }
@@ -598,9 +642,6 @@ int nusi_points_count(const nusi_points *p) { return p ? p->n : 0; }
 // integrator's CTAs displace builder CTAs one for one -- and it blurs the per-kernel event times.  By default
 // all kernels run on the caller's stream in order.
 // ------------------------------------------------------------------------------------------------------
-#ifndef NUSI_SLICE
-#define NUSI_SLICE 2048
-#endif
 static int ensure_streams(nusi_ctx *c) {
   if (c->s_x) return NUSI_OK;
   int lo = 0, hi = 0;
@@ -659,7 +700,10 @@ static int run_pipeline(nusi_ctx *c, const nusi_points *p, double *d_fm, double 
     if ((rc = launch_rows(c, p->d_params + off, cnt, d_st + off, W, si))) return rc;
     CU(cudaEventRecord(t6[1], si));
     CU(cudaEventRecord(t6[2], sx));
-    if ((rc = launch_alpha(c, p->d_params + off, cnt, d_st + off, W, sx))) return rc;
+    const bool grouped = (p->SL == SL) && p->d_groups && k + 1 < p->slice_g0.size();
+    if ((rc = launch_alpha(c, p->d_params + off, cnt, d_st + off, W, sx, grouped ? p->d_groups + p->slice_g0[k] : nullptr,
+                           grouped ? p->slice_g0[k + 1] - p->slice_g0[k] : 0)))
+      return rc;
     CU(cudaEventRecord(t6[3], sx));
     if (overlap) {
       CU(cudaEventRecord(ev_tab, sx));
@@ -756,29 +800,35 @@ int nusi_tables_batch(nusi_ctx *c, int n, const double *mphi, const double *g, c
   c->ev_used = 0;
   c->n_launches = 0;
   std::vector<double> hrows((size_t)2 * NT), htri(c->tstride);
-  for (int i = 0; i < n && rc == NUSI_OK; ++i) {
-    rc = ensure_workspace(c, 1);
+  // group by group, through the same builder a batch of these points gets in nusi_evolve_batch
+  for (size_t gi = 0; gi < p->h_groups.size() && rc == NUSI_OK; ++gi) {
+    const int i0 = p->h_groups[gi].x, len = p->h_groups[gi].y;
+    rc = ensure_workspace(c, len);
     if (rc) break;
     const WorkSlot W = work_slot(c, 0);
-    rc = launch_rows(c, p->d_params + i, 1, p->d_status0 + i, W, nullptr);
-    if (rc == NUSI_OK) rc = launch_alpha(c, p->d_params + i, 1, p->d_status0 + i, W, nullptr);
+    rc = launch_rows(c, p->d_params + i0, len, p->d_status0 + i0, W, nullptr);
+    if (rc == NUSI_OK)
+      rc = launch_alpha(c, p->d_params + i0, len, p->d_status0 + i0, W, nullptr, c->d_unit_groups ? c->d_unit_groups + len : nullptr, 1);
     if (rc) break;
-    cudaError_t e = cudaMemcpy(hrows.data(), c->d_rows, hrows.size() * sizeof(double), cudaMemcpyDeviceToHost);
-    if (e == cudaSuccess) e = cudaMemcpy(htri.data(), c->d_tri, htri.size() * sizeof(double), cudaMemcpyDeviceToHost);
-    if (e != cudaSuccess) {
-      rc = fail(NUSI_E_CUDA, std::string("tables_batch: ") + cudaGetErrorString(e));
-      break;
-    }
-    if (Gamma) std::memcpy(Gamma + (size_t)i * NT, hrows.data(), NT * sizeof(double));
-    if (alphaTilde) std::memcpy(alphaTilde + (size_t)i * NT, hrows.data() + NT, NT * sizeof(double));
-    if (alpha) {
-      double *A = alpha + (size_t)i * NT * NT;
-      std::memset(A, 0, (size_t)NT * NT * sizeof(double));
-      if (c->G.non_resonant) {
-        for (int b = 1; b < NT; ++b)
-          for (int a = 0; a < b; ++a) A[(size_t)a * NT + b] = htri[(size_t)b * (b - 1) / 2 + a];
-      } else {
-        for (int a = 0; a + 1 < NT; ++a) A[(size_t)a * NT + a + 1] = htri[a];
+    for (int i = i0; i < i0 + len; ++i) {
+      cudaError_t e = cudaMemcpy(hrows.data(), c->d_rows + (size_t)(i - i0) * 2 * NT, hrows.size() * sizeof(double), cudaMemcpyDeviceToHost);
+      if (e == cudaSuccess)
+        e = cudaMemcpy(htri.data(), c->d_tri + (size_t)(i - i0) * c->tstride, htri.size() * sizeof(double), cudaMemcpyDeviceToHost);
+      if (e != cudaSuccess) {
+        rc = fail(NUSI_E_CUDA, std::string("tables_batch: ") + cudaGetErrorString(e));
+        break;
+      }
+      if (Gamma) std::memcpy(Gamma + (size_t)i * NT, hrows.data(), NT * sizeof(double));
+      if (alphaTilde) std::memcpy(alphaTilde + (size_t)i * NT, hrows.data() + NT, NT * sizeof(double));
+      if (alpha) {
+        double *A = alpha + (size_t)i * NT * NT;
+        std::memset(A, 0, (size_t)NT * NT * sizeof(double));
+        if (c->G.non_resonant) {
+          for (int b = 1; b < NT; ++b)
+            for (int a = 0; a < b; ++a) A[(size_t)a * NT + b] = htri[(size_t)b * (b - 1) / 2 + a];
+        } else {
+          for (int a = 0; a + 1 < NT; ++a) A[(size_t)a * NT + a + 1] = htri[a];
+        }
       }
     }
   }

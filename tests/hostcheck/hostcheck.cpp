@@ -42,7 +42,9 @@ void hc_tables(double mphi, double g, double Ga, const double *mn, const double 
     if (alphaTilde) alphaTilde[i] = nusi::alphatilde_row(P, nullptr, lo[i], hi[i], warn);
     if (alpha)
       for (int m = i + 1; m < NT; ++m)
-        alpha[(size_t)i * NT + m] = (majorana && non_resonant && hc_shared_logs == 3)
+        alpha[(size_t)i * NT + m] = (majorana && non_resonant && !phiphi && hc_shared_logs == 4)
+                                        ? nusi::alpha_entry_grouped(P, lo[i], hi[i], lo[m], hi[m], warn)
+                                    : (majorana && non_resonant && hc_shared_logs == 3)
                                         ? nusi::alpha_entry_compact<true>(P, nullptr, lo[i], hi[i], lo[m], hi[m], warn)
                                     : (majorana && non_resonant && hc_shared_logs == 2)
                                         ? nusi::alpha_entry_compact<false>(P, nullptr, lo[i], hi[i], lo[m], hi[m], warn)

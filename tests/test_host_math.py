@@ -95,3 +95,15 @@ def test_cross_section_tables_vs_oracle(hc, oracle, mphi, g, maj, nr, no):
         rs = oracle.relerr(Ts, T0)[iu]
         assert np.median(rs) < 2e-11
         assert np.mean(rs < 1e-9) > (0.80 if mphi < 500 else 0.60)
+
+
+@pytest.mark.parametrize("mphi,g,no", [(100.0, 1e-2, 1), (30.0, 1e-1, 1), (1e3, 1e-2, 1), (300.0, 1.0, 0), (1e4, 1e-3, 1), (10.0, 1e-5, 0)])
+def test_grouped_scan_split_equals_compact_bitwise(hc, oracle, mphi, g, no):
+    """The grouped scan builder evaluates a table entry as a g-independent part (shared by all points with the
+    same mphi and neutrino masses) plus a per-g part.  The cut must not change a single bit of the compact
+    builder's entry (alpha_entry_compact<true>)."""
+    _, _, T3 = _tables(hc, oracle, mphi, g, 1, 1, no, shared=3)
+    _, _, T4 = _tables(hc, oracle, mphi, g, 1, 1, no, shared=4)
+    iu = np.triu_indices(T3.shape[0], 1)
+    assert np.array_equal(T3[iu].view(np.uint64), T4[iu].view(np.uint64))
+    assert np.all(np.isfinite(T4[iu])) and np.any(T4[iu] != 0)
