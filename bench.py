@@ -189,24 +189,30 @@ def workload_config(gpus):
 
 
 def roofline(nb, device, flops_table_per_point, points, steps, ms_alpha_total):
-    """The dominant kernel (alpha table builder) against the FP64 pipe.
+    """The dominant kernel (alpha table builder; alpha_group_kernel on a scan) against the FP64 pipe.
     achieved = SURVEY 8(d) census (13.9 kflop per table entry of the reference's per-entry formulation) x entries
-    x points / CUDA-event time of the kernel, measured live.  The tiled kernel shares vertex work between
-    entries, so it executes fewer flops than the census counts: frac is "reference-equivalent work per second /
-    peak" and can exceed 1.  fp64_pipe_pct is the measured pipe utilisation of the same kernel (ncu
-    sm__pipe_fp64_cycles_active, committed capture); traffic = ncu dram bytes read + written, scaled from the
-    captured launch to this launch's point count."""
+    x points / CUDA-event time of the kernel, measured live.  The kernel shares vertex work between entries and
+    g-independent work between the points of a (mphi, m_nu) group, so it EXECUTES far fewer flops than the census
+    counts: frac is "reference-equivalent work per second / peak" and exceeds 1.  What the pipe really does is in
+    executed_tflops / executed_frac (FP64 flops the kernel executes per point, from the committed ncu capture:
+    2 x DFMA + DMUL + DADD thread instructions, x points / live kernel time, / live DFMA peak) and fp64_pipe_pct
+    (ncu sm__pipe_fp64_cycles_active of the same capture).  traffic = ncu dram bytes read + written, scaled from
+    the captured launch to this launch's point count."""
     peak = nb.measure_fp64_peak(device)
     ach = (flops_table_per_point * points * steps) / (ms_alpha_total * 1e-3) / 1e12 if ms_alpha_total > 0 else None
-    r = {"bound": "fp64", "kernel": "alpha_compact_kernel", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
-         "frac": (ach / peak) if ach else None, "traffic": None, "fp64_pipe_pct": None,
+    r = {"bound": "fp64", "kernel": "alpha_group_kernel", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+         "frac": (ach / peak) if ach else None, "traffic": None, "fp64_pipe_pct": None, "executed_tflops": None, "executed_frac": None,
          "note": "peak = DFMA rate measured in this run (MEASURED_PEAKS.json has no FP64 figure); achieved = algorithmic census "
-                 "(13.9 kflop x NT(NT-1)/2 entries x points) / CUDA-event kernel time; the kernel executes fewer flops than the census "
-                 "(vertices shared between entries), so see fp64_pipe_pct for the measured pipe utilisation"}
+                 "(13.9 kflop x NT(NT-1)/2 entries x points) / CUDA-event kernel time, i.e. reference-equivalent work: the kernel "
+                 "executes far fewer flops (vertices shared between entries, g-independent work shared between the points of a "
+                 "scan row), so frac > 1; executed_tflops / executed_frac / fp64_pipe_pct are what the FP64 pipe really does"}
     try:
-        k = json.load(open(os.path.join(ROOT, "profiles", "ncu_roofline.json")))["alpha_compact_kernel"]
+        k = json.load(open(os.path.join(ROOT, "profiles", "ncu_roofline.json")))["alpha_group_kernel"]
         r["traffic"] = (k["dram_bytes_read"] + k["dram_bytes_write"]) / k["points_in_capture"] * points
         r["fp64_pipe_pct"] = k["fp64_pipe_pct"]
+        if k.get("fp64_flop") and ms_alpha_total > 0:
+            r["executed_tflops"] = k["fp64_flop"] / k["points_in_capture"] * points * steps / (ms_alpha_total * 1e-3) / 1e12
+            r["executed_frac"] = r["executed_tflops"] / peak
         r["ncu_source"] = k["source"]
     except Exception:
         pass

@@ -294,6 +294,8 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
       for (int L = 0; L <= NUSI_GROUP_CAP; ++L) unit.push_back(make_int2(0, L));
       if (e1 == cudaSuccess) e1 = upload(unit, &c->d_unit_groups);
       if (e1 == cudaSuccess)
+        e1 = cudaFuncSetAttribute(alpha_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GroupSmem));
+      if (e1 == cudaSuccess)
         e1 = cudaFuncSetAttribute(alpha_tile_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem));
       if (e1 == cudaSuccess)
         e1 = cudaFuncSetAttribute(alpha_tile_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem));
@@ -483,7 +485,7 @@ static int launch_alpha(nusi_ctx *c, const PointParams *d_params, int cnt, int *
     if (mode >= 3 && d_groups && ngroups > 0 && !G.phiphi) {
       // scan builder: one CTA per (tile, group of points with the same mphi and neutrino masses)
       dim3 gg(c->n_ctiles, ngroups);
-      alpha_group_kernel<<<gg, 256, 0, s>>>(G, c->n_edges, d_params, W.edges, c->d_ctiles, d_groups, W.tri, c->tstride, d_status);
+      alpha_group_kernel<<<gg, 256, sizeof(GroupSmem), s>>>(G, c->n_edges, d_params, W.edges, c->d_ctiles, d_groups, W.tri, c->tstride, d_status);
     } else if (mode >= 2) {
       dim3 gc(c->n_ctiles, cnt);
       alpha_compact_kernel<<<gc, 256, 0, s>>>(G, c->n_edges, d_params, W.edges, c->d_ctiles, W.tri, c->tstride, d_status);

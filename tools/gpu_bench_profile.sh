@@ -9,7 +9,7 @@ ARGS="--points 296 --steps 2 --warmup 1 --no-cpu-baseline"
 python bench.py $ARGS > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches.csv python bench.py $ARGS > gpurun_out/ncu_launch.log 2>&1
 echo "ncu launches exit=$?"
-for K in alpha_compact integrate_diag "rows_kernel<1>" "rows_kernel<0>"; do
+for K in alpha_group integrate_diag "rows_kernel<1>" "rows_kernel<0>"; do
   ncu --set full --clock-control none --import-source on -k regex:"$K" -s 1 -c 1 -f -o "gpurun_out/prof_${K//[<>]/}" python bench.py $ARGS > gpurun_out/"ncu_full_${K//[<>]/}.log" 2>&1
   echo "ncu full $K exit=$?"
 done
