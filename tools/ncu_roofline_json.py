@@ -17,8 +17,11 @@ for arg in sys.argv[2:]:
                  "issue_active_per_cycle": float(d['smsp__issue_active.avg.per_cycle_active']),
                  "registers_per_thread": int(float(d['launch__registers_per_thread'])),
                  "warp_inst": float(d['smsp__inst_executed.sum'].replace(',', '')),
-                 "fp64_flop": 2 * val('smsp__sass_thread_inst_executed_op_dfma_pred_on.sum') + val('smsp__sass_thread_inst_executed_op_dmul_pred_on.sum')
-                 + val('smsp__sass_thread_inst_executed_op_dadd_pred_on.sum'),
+                 # FP64 flops the launch executed: (2 DFMA + DMUL + DADD) thread instructions per elapsed cycle x elapsed cycles
+                 "fp64_flop": (2 * float(d['smsp__sass_thread_inst_executed_op_dfma_pred_on.sum.per_cycle_elapsed'].replace(',', ''))
+                               + float(d['smsp__sass_thread_inst_executed_op_dmul_pred_on.sum.per_cycle_elapsed'].replace(',', ''))
+                               + float(d['smsp__sass_thread_inst_executed_op_dadd_pred_on.sum.per_cycle_elapsed'].replace(',', '')))
+                 * float(d['smsp__cycles_elapsed.avg'].replace(',', '')),
                  "source": "ncu --set full --clock-control none, bench.py --points 296 --steps 2 --warmup 1 (profiles/%s_*)" % tag}
 json.dump(out, open("profiles/ncu_roofline.json", "w"), indent=1)
 print(json.dumps(out, indent=1))
