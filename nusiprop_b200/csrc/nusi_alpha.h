@@ -635,6 +635,8 @@ NUSI_HD void alpha_cell_mass_compact(const CellConst &K, const PhiPhiTables *pp,
 // (mphi, m_nu) group and combined per g reproduce it bit for bit.
 struct CellShared {
   double X, Y;
+  double GL;  // the t channel's Gauss-Legendre fallback integral (nuSIprop.hpp:1288-1303), evaluated only where X < 0:
+              // a_t = prefactor * X can be negative (prefactor >= 0) only there
 };
 NUSI_HD void alpha_cell_shared(const CellLogs &L, const RowEdge &Rm, const RowEdge &Rp, const ColEdge &Cm,
                                const ColEdge &Cp, double l1mm, double l1pm, double l1mp, double l1pp, double Hs,
@@ -656,10 +658,11 @@ NUSI_HD void alpha_cell_shared(const CellLogs &L, const RowEdge &Rm, const RowEd
          sm * sp * (1 + tm) * (1 + tp) *
              ((Cp.ls + l1mm) * (Cm.ls2 + Rm.l1m - Rm.labs) + (Cm.ls + l1pm) * (Cp.l2s - Rm.l1m + Rm.labs)) +
          sm * sp * (lpm + l1mp - l1pp) * (2 * tm + (1 + tm) * (1 + tp) * Rp.labs) + sm * sp * (1 + tm) * (1 + tp) * Hs);
+  O.GL = (O.X < 0) ? alpha_gl2d<0>(tp, tm, sm, sp) : 0.0;
 }
 NUSI_HD void alpha_cell_combine(const CellConst &K, double wgt, double U2, double fs, const RowEdge &Rm,
-                                const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, double X, double Y, double Gs,
-                                double &tot, int *warn) {
+                                const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, double X, double Y, double GL,
+                                double Gs, double &tot, int *warn) {
   const double g4 = K.g4, m4 = K.m4, gr = K.gr;
   const double tm = Rm.t, tp = Rp.t, sm = Cm.s, sp = Cp.s;
 
@@ -668,7 +671,7 @@ NUSI_HD void alpha_cell_combine(const CellConst &K, double wgt, double U2, doubl
   tot += wgt * a_s;
 
   double a_t = K.c_t * (Cm.is * Cp.is) * X;
-  if (a_t < 0) a_t = alpha_gl2d<0>(tp, tm, sm, sp) * (g4 / (16 * kPi * m4));
+  if (a_t < 0) a_t = GL * (g4 / (16 * kPi * m4));
   a_t *= U2;
   tot += wgt * a_t;
   tot += wgt * a_t;  // u channel = t channel for Majorana
@@ -826,7 +829,7 @@ NUSI_HD double alpha_entry_grouped(const PointParams &P, double Em, double Ep, d
     alpha_cell_shared(L, Rm, Rp, Cm, Cp, Vmm.l1, Vpm.l1, Vmp.l1, Vpp.l1, Vmm.H - Vpm.H - Vmp.H + Vpp.H, O);
     const double Gmm = make_vertex_compact_G(Rm, Cm, gr, Vmm.l1, Vmm.zr_re), Gpm = make_vertex_compact_G(Rm, Cp, gr, Vpm.l1, Vpm.zr_re);
     const double Gmp = make_vertex_compact_G(Rp, Cm, gr, Vmp.l1, Vmp.zr_re), Gpp = make_vertex_compact_G(Rp, Cp, gr, Vpp.l1, Vpp.zr_re);
-    alpha_cell_combine(K, K.m4 / (2 * P.mn[k]), P.U2f[k], alpha_s_colfactor(P, sm, sp), Rm, Rp, Cm, Cp, O.X, O.Y,
+    alpha_cell_combine(K, K.m4 / (2 * P.mn[k]), P.U2f[k], alpha_s_colfactor(P, sm, sp), Rm, Rp, Cm, Cp, O.X, O.Y, O.GL,
                        Gmm - Gpm - Gmp + Gpp, tot, warn);
   }
   return tot;
