@@ -461,9 +461,21 @@ static WorkSlot work_slot(const nusi_ctx *c, int wo) {
 }
 
 // Gamma / alphaTilde rows of `cnt` points
-static int launch_rows(nusi_ctx *c, const PointParams *d_params, int cnt, int *d_status, const WorkSlot &W, cudaStream_t s) {
+static int launch_rows(nusi_ctx *c, const PointParams *d_params, int cnt, int *d_status, const WorkSlot &W, cudaStream_t s,
+                       const int2 *d_groups = nullptr, int ngroups = 0) {
   const DeviceGrid &G = c->G;
   dim3 gr((G.NT + NUSI_ROWS_PER_CTA - 1) / NUSI_ROWS_PER_CTA, cnt);
+  const char *mode_env = getenv("NUSI_ALPHA_MODE");
+  const int mode = mode_env ? atoi(mode_env) : c->opt.elementary_mode;
+  if (mode >= 3 && d_groups && ngroups > 0 && G.majorana && G.non_resonant && !G.phiphi && !getenv("NUSI_ROWS_UNGROUPED")) {
+    const char *rs = getenv("NUSI_ROWS_SPLIT");
+    dim3 gg(gr.x, ngroups, rs && atoi(rs) > 0 ? atoi(rs) : 4);  // scan: the g-independent part of a row once per (part of a) group
+    rows_group_kernel<0><<<gg, NUSI_ROWS_PER_CTA * 3, 0, s>>>(G, d_params, d_groups, W.rows, d_status);
+    rows_group_kernel<1><<<gg, NUSI_ROWS_PER_CTA * 3, 0, s>>>(G, d_params, d_groups, W.rows, d_status);
+    c->n_launches += 2;
+    CU(cudaGetLastError());
+    return NUSI_OK;
+  }
   rows_kernel<0><<<gr, NUSI_ROWS_PER_CTA * 3, 0, s>>>(G, d_params, W.rows, d_status);
   rows_kernel<1><<<gr, NUSI_ROWS_PER_CTA * 3, 0, s>>>(G, d_params, W.rows, d_status);
   c->n_launches += 2;
@@ -699,10 +711,12 @@ static int run_pipeline(nusi_ctx *c, const nusi_points *p, double *d_fm, double 
       CU(cudaStreamWaitEvent(sx, c->ev_ji, 0));
     }
     CU(cudaEventRecord(t6[0], si));
-    if ((rc = launch_rows(c, p->d_params + off, cnt, d_st + off, W, si))) return rc;
+    const bool grouped = (p->SL == SL) && p->d_groups && k + 1 < p->slice_g0.size();
+    if ((rc = launch_rows(c, p->d_params + off, cnt, d_st + off, W, si, grouped ? p->d_groups + p->slice_g0[k] : nullptr,
+                          grouped ? p->slice_g0[k + 1] - p->slice_g0[k] : 0)))
+      return rc;
     CU(cudaEventRecord(t6[1], si));
     CU(cudaEventRecord(t6[2], sx));
-    const bool grouped = (p->SL == SL) && p->d_groups && k + 1 < p->slice_g0.size();
     if ((rc = launch_alpha(c, p->d_params + off, cnt, d_st + off, W, sx, grouped ? p->d_groups + p->slice_g0[k] : nullptr,
                            grouped ? p->slice_g0[k + 1] - p->slice_g0[k] : 0)))
       return rc;
@@ -808,7 +822,7 @@ int nusi_tables_batch(nusi_ctx *c, int n, const double *mphi, const double *g, c
     rc = ensure_workspace(c, len);
     if (rc) break;
     const WorkSlot W = work_slot(c, 0);
-    rc = launch_rows(c, p->d_params + i0, len, p->d_status0 + i0, W, nullptr);
+    rc = launch_rows(c, p->d_params + i0, len, p->d_status0 + i0, W, nullptr, c->d_unit_groups ? c->d_unit_groups + len : nullptr, 1);
     if (rc == NUSI_OK)
       rc = launch_alpha(c, p->d_params + i0, len, p->d_status0 + i0, W, nullptr, c->d_unit_groups ? c->d_unit_groups + len : nullptr, 1);
     if (rc) break;

@@ -136,6 +136,116 @@ NUSI_HD int gamma_mass(const PointParams &P, int j, double Em, double Ep, double
   return NUSI_GAMMA_NCH;
 }
 
+// ---- split for parameter scans (Majorana, non-resonant, phiphi off) ---------------------------------
+// gamma_mass() cut into the part that does not contain g (shared by all points of a scan row with the same
+// mphi and neutrino masses) and the per-point rest.  Same operations on the same operands in the same order,
+// so gamma_mass_point(gamma_mass_shared()) reproduces gamma_mass() bit for bit (tests/test_host_math.py, and
+// tests/test_gpu_parity.py for the kernels).  Prefactors are >= 0, so a closed form can only come out negative
+// where its g-independent bracket is negative: the Gauss-Legendre fallbacks are evaluated there, once.
+struct GammaShared {
+  double splus, sminus, l1p, l1m;
+  double B1, GL1;  // t+u bracket, its fallback integral (where B1 < 0)
+  double B2, GL2;  // t-u interference bracket, its fallback
+  double dd;       // dilogdiff(splus, sminus)
+};
+NUSI_HD void gamma_mass_shared(double mphi, double mnj, double Em, double Ep, GammaShared &S) {
+  const double splus = 2 * mnj * Ep / sqr(mphi);
+  const double sminus = 2 * mnj * Em / sqr(mphi);
+  S.splus = splus;
+  S.sminus = sminus;
+  const double l1p = nlog1p(splus), l1m = nlog1p(sminus);
+  S.l1p = l1p;
+  S.l1m = l1m;
+  S.B1 = (2 * l1p / splus - 2 * l1m / sminus + l1p - l1m);
+  S.GL1 = (S.B1 < 0) ? gl3<gamma_tu_sum_integrand>(sminus, splus) : 0.0;
+  S.dd = dilogdiff(splus, sminus);
+  S.B2 = (sminus * l1p * (2 + 2 * splus + splus * nlog(2 + splus)) -
+          splus * l1m * (2 + 2 * sminus + sminus * nlog(2 + sminus)) +
+          sminus * splus * (dilog1mdiff(splus, sminus) + S.dd));
+  S.GL2 = (S.B2 < 0) ? gl3<gamma_tu_intf_integrand>(sminus, splus) : 0.0;
+}
+NUSI_HD int gamma_mass_point(const PointParams &P, int j, const GammaShared &S, double *ch, int *warn) {
+  const double mphi = P.mphi, g = P.g, Ga = P.Ga;
+  const double g4 = sqr(sqr(g));
+  const double U2 = P.U2f[j];
+  const double wgt = sqr(mphi) / (2 * P.mn[j]);
+  const double splus = S.splus, sminus = S.sminus;
+
+  const double bw = sqr(mphi) / (sqr(mphi) + sqr(Ga));
+  const double dlog = nlog1p(bw * splus * (splus - 2)) - nlog1p(bw * sminus * (sminus - 2));
+  double Gs;
+  if (splus < 1e-5) {
+    const double gr = Ga / mphi;
+    Gs = g4 / (32 * kPi * sqr(mphi) * Ga) *
+         (2 * mphi *
+              ((gr * (1 + sqr(gr) + 2 * sminus)) / sqr(1 + sqr(gr)) * (splus - sminus) +
+               (gr) / sqr(1 + sqr(gr)) * sqr(splus - sminus)) +
+          Ga * dlog);
+  } else {
+    Gs = g4 / (32 * kPi * sqr(mphi) * Ga) *
+         (2 * mphi * atandiff(mphi * (splus - 1) / Ga, mphi * (sminus - 1) / Ga) + Ga * dlog);
+  }
+  Gs *= U2;
+  ch[0] = wgt * Gs;
+
+  const double l1p = S.l1p, l1m = S.l1m;
+
+  double Gtu_sum = g4 / (16 * kPi * sqr(mphi)) * S.B1;
+  if (Gtu_sum < 0) Gtu_sum = g4 / (16 * kPi * sqr(mphi)) * S.GL1;
+  Gtu_sum *= 2 * U2;
+  ch[1] = wgt * Gtu_sum;
+
+  double Gtu = g4 / (32 * kPi * sqr(mphi) * sminus * splus) * S.B2;
+  if (Gtu < 0) Gtu = g4 / (16 * kPi * sqr(mphi)) * S.GL2;
+  Gtu *= U2;  // Majorana
+  ch[2] = wgt * Gtu;
+
+  const double gr = Ga / mphi;
+  const cplx den = mk(gr, 2.0);
+  const cplx z1p = mk(0.0, 1 + splus) / den;
+  const cplx z1m = mk(0.0, 1 + sminus) / den;
+  const cplx z2p = conj(z1p), z2m = conj(z1m);
+  cplx dd1, dd2;
+  if (splus < 1e-5) {
+    const cplx ip = mk(gr, 1.0), im = mk(gr, -1.0);
+    const cplx c1 = clog_(ip / den);
+    const cplx c2 = clog_(im / mk(gr, -2.0));
+    const cplx I = mk(0.0, 1.0);
+    dd1 = sqr(sminus) * ((-(I / 2.0)) / ip - c1 / 2.) + sminus * c1 - splus * c1 +
+          (sqr(splus) * (I / ip + c1)) / 2.;
+    dd2 = sqr(sminus) * ((I / 2.0) / im - c2 / 2.) + sminus * c2 - splus * c2 +
+          (sqr(splus) * ((-I) / im + c2)) / 2.;
+  } else {
+    dd1 = dilogdiff_complex(z1p, z1m);
+    dd2 = dilogdiff_complex(z2p, z2m);
+  }
+  const double lam_p = nlog1p(sqr(-1 + splus) / sqr(gr)), lam_m = nlog1p(sqr(-1 + sminus) / sqr(gr));
+  double Gst = -g4 / (32 * kPi * sqr(mphi) * (1 + sqr(gr))) *
+               (dd1.re + dd2.re + gr * (dd2.im - dd1.im) + 2 * gr * carg_(1.0 - z2p) * l1p -
+                2 * gr * carg_(1.0 - z2m) * l1m + nlog1p(4 / sqr(gr)) * (l1m - l1p) + lam_p * l1p -
+                lam_m * l1m + (1 + sqr(gr)) * (lam_m - lam_p) + 2 * S.dd);
+  Gst *= U2;
+  ch[3] = wgt * Gst;
+  const double Gsu = Gst;  // Majorana
+  ch[4] = wgt * Gsu;
+  const double Gpp = 0;  // phiphi off
+  ch[5] = wgt * Gpp;
+
+  if (warn && (Gs < 0 || Gtu_sum < 0 || Gtu < 0 || (Gs + Gtu_sum + Gst + Gsu) < 0)) *warn |= 1;
+  return NUSI_GAMMA_NCH;
+}
+NUSI_HD double gamma_row_split(const PointParams &P, double Em, double Ep, int *warn) {
+  double tot = 0;
+  for (int j = 0; j < 3; ++j) {
+    double ch[NUSI_GAMMA_NCH];
+    GammaShared S;
+    gamma_mass_shared(P.mphi, P.mn[j], Em, Ep, S);
+    const int n = gamma_mass_point(P, j, S, ch, warn);
+    for (int c = 0; c < n; ++c) tot += ch[c];
+  }
+  return tot;
+}
+
 // Gamma(Em, Ep) = sum over the three target masses, accumulated in mass order like the reference
 NUSI_HD double gamma_row(const PointParams &P, double Em, double Ep, int *warn) {
   double tot = 0;

@@ -38,8 +38,10 @@ void hc_tables(double mphi, double g, double Ga, const double *mn, const double 
   P.majorana = majorana; P.non_resonant = non_resonant; P.phiphi = phiphi;
   *warn = 0;
   for (int i = 0; i < NT; ++i) {
-    if (Gamma) Gamma[i] = nusi::gamma_row(P, lo[i], hi[i], warn);
-    if (alphaTilde) alphaTilde[i] = nusi::alphatilde_row(P, nullptr, lo[i], hi[i], warn);
+    const bool split = majorana && non_resonant && !phiphi && hc_shared_logs == 4;
+    if (Gamma) Gamma[i] = split ? nusi::gamma_row_split(P, lo[i], hi[i], warn) : nusi::gamma_row(P, lo[i], hi[i], warn);
+    if (alphaTilde)
+      alphaTilde[i] = split ? nusi::alphatilde_row_split(P, lo[i], hi[i], warn) : nusi::alphatilde_row(P, nullptr, lo[i], hi[i], warn);
     if (alpha)
       for (int m = i + 1; m < NT; ++m)
         alpha[(size_t)i * NT + m] = (majorana && non_resonant && !phiphi && hc_shared_logs == 4)

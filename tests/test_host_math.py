@@ -102,8 +102,10 @@ def test_grouped_scan_split_equals_compact_bitwise(hc, oracle, mphi, g, no):
     """The grouped scan builder evaluates a table entry as a g-independent part (shared by all points with the
     same mphi and neutrino masses) plus a per-g part.  The cut must not change a single bit of the compact
     builder's entry (alpha_entry_compact<true>)."""
-    _, _, T3 = _tables(hc, oracle, mphi, g, 1, 1, no, shared=3)
-    _, _, T4 = _tables(hc, oracle, mphi, g, 1, 1, no, shared=4)
+    G3, A3, T3 = _tables(hc, oracle, mphi, g, 1, 1, no, shared=3)
+    G4, A4, T4 = _tables(hc, oracle, mphi, g, 1, 1, no, shared=4)
+    assert np.array_equal(G3.view(np.uint64), G4.view(np.uint64)) and np.array_equal(A3.view(np.uint64), A4.view(np.uint64))
+    assert np.all(np.isfinite(G4)) and np.all(np.isfinite(A4)) and np.any(G4 != 0) and np.any(A4 != 0)
     iu = np.triu_indices(T3.shape[0], 1)
     assert np.array_equal(T3[iu].view(np.uint64), T4[iu].view(np.uint64))
     assert np.all(np.isfinite(T4[iu])) and np.any(T4[iu] != 0)
