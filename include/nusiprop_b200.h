@@ -59,10 +59,14 @@ typedef struct nusi_opts {
   int elementary_mode;   /* alpha builder (Majorana, non_resonant):
                             0 = strict: every log/arg evaluated where the reference evaluates it;
                             1 = the logs/args of a table vertex are formed from one vertex log plus per-edge logs;
-                            2 (default) = 1 + per-vertex grouping of the s-t / t-u interference sums, 16x16-vertex
-                                tiles, all three target masses per barrier (same closed forms; fastest).
+                            2 = 1 + per-vertex grouping of the s-t / t-u interference sums, 16x16-vertex
+                                tiles, all three target masses per barrier (same closed forms);
+                            3 (default) = 2, and runs of consecutive points with identical (mphi, mntot) -- the rows
+                                of a (mphi, g) scan -- share everything that does not depend on g (evaluated once
+                                per run, at most 32 points); bitwise identical to mode 2, 2.9x faster on a scan.
+                                Put the points of a scan in mphi-major order to profit; any order is correct.
                             Parity with the reference is at the reference's own FMA-on/off noise floor in all
-                            three modes. */
+                            all modes. */
   int source_model;      /* 0 (default) = the reference's source: diffuse supernova background, Fermi-Dirac spectrum
                                 (nuSIprop.hpp:638-662; si and norm are inert there);
                             1 = power law of the upstream code that the reference keeps commented out (:648-657):
