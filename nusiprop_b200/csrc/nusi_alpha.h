@@ -664,7 +664,7 @@ NUSI_HD void alpha_cell_combine(const CellConst &K, double wgt, double U2, doubl
                                 const RowEdge &Rp, const ColEdge &Cm, const ColEdge &Cp, double X, double Y, double GL,
                                 double Gs, double &tot, int *warn) {
   const double g4 = K.g4, m4 = K.m4, gr = K.gr;
-  const double tm = Rm.t, tp = Rp.t, sm = Cm.s, sp = Cp.s;
+  const double tm = Rm.t, tp = Rp.t;
 
   double a_s = K.c_s * (tm - tp) * fs;
   a_s *= U2;

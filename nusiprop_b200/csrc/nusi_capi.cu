@@ -53,6 +53,8 @@ struct nusi_ctx {
   double *d_edgeE = nullptr;  // distinct bin-edge energies of the table cells (tiled builder)
   int2 *d_tiles = nullptr;
   int n_tiles = 0;
+  unsigned char *d_pool = nullptr;  // points block of nusi_evolve_batch, kept across calls
+  size_t pool_cap = 0;
   int2 *d_unit_groups = nullptr;  // (0, L) for L = 0..NUSI_GROUP_CAP: one-group launches of the scan builder
   int4 *d_ctiles = nullptr;  // compact builder: per tile the cell ranges [a0, a1) x [b0, b1) of its row / column segment
   int n_ctiles = 0;
@@ -87,6 +89,8 @@ struct nusi_points {
   // scan builder (elementary_mode 3): runs of consecutive points with identical (mphi, m_nu), cut at slice boundaries
   // and at NUSI_GROUP_MAX points; (first point relative to its slice, length)
   int2 *d_groups = nullptr;
+  unsigned char *d_block = nullptr;  // the one device allocation behind d_params / d_groups / d_status0
+  bool pooled = false;               // d_block belongs to the context (nusi_evolve_batch)
   std::vector<int2> h_groups;  // host copy with ABSOLUTE first point (nusi_tables_batch)
   std::vector<int> slice_g0;  // slice k owns groups [slice_g0[k], slice_g0[k+1])
   int SL = 0;                 // the slice length the groups were cut for
@@ -152,6 +156,7 @@ void nusi_ctx_destroy(nusi_ctx *c) {
   if (c->d_tiles) cudaFree(c->d_tiles);
   if (c->d_ctiles) cudaFree(c->d_ctiles);
   if (c->d_unit_groups) cudaFree(c->d_unit_groups);
+  if (c->d_pool) cudaFree(c->d_pool);
   for (double *p : ptrs)
     if (p) cudaFree(p);
   for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
@@ -596,8 +601,11 @@ static int launch_integrate(nusi_ctx *c, const PointParams *d_params, int cnt, d
   return NUSI_OK;
 }
 
-int nusi_points_create(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
-                       nusi_points **out) {
+// One device block per points object: [params | groups | status0], filled by ONE host->device copy.  pooled: the block
+// is the context's own (grown on demand, kept across calls) -- nusi_evolve_batch, which would otherwise pay three
+// cudaMalloc + three cudaFree (each a device synchronisation) per call.
+static int points_create_impl(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
+                              nusi_points **out, bool pooled) {
   if (!c || !out || n <= 0 || !mphi || !g || !mntot) return NUSI_E_INVALID;
   CU(cudaSetDevice(c->opt.device));
   std::vector<PointParams> pp;
@@ -625,12 +633,35 @@ int nusi_points_create(nusi_ctx *c, int n, const double *mphi, const double *g, 
     }
     p->slice_g0.push_back((int)groups.size());
   }
-  cudaError_t e = cudaMalloc((void **)&p->d_params, (size_t)n * sizeof(PointParams));
-  if (e == cudaSuccess) e = cudaMalloc((void **)&p->d_status0, (size_t)n * sizeof(int));
-  if (e == cudaSuccess) e = cudaMalloc((void **)&p->d_groups, groups.size() * sizeof(int2));
-  if (e == cudaSuccess) e = cudaMemcpy(p->d_groups, groups.data(), groups.size() * sizeof(int2), cudaMemcpyHostToDevice);
-  if (e == cudaSuccess) e = cudaMemcpy(p->d_params, pp.data(), (size_t)n * sizeof(PointParams), cudaMemcpyHostToDevice);
-  if (e == cudaSuccess) e = cudaMemcpy(p->d_status0, p->h_status0.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice);
+  const size_t o_groups = ((size_t)n * sizeof(PointParams) + 15) & ~(size_t)15;
+  const size_t o_status = o_groups + ((groups.size() * sizeof(int2) + 15) & ~(size_t)15);
+  const size_t bytes = o_status + (size_t)n * sizeof(int);
+  std::vector<unsigned char> stage(bytes);
+  std::memcpy(stage.data(), pp.data(), (size_t)n * sizeof(PointParams));
+  std::memcpy(stage.data() + o_groups, groups.data(), groups.size() * sizeof(int2));
+  std::memcpy(stage.data() + o_status, p->h_status0.data(), (size_t)n * sizeof(int));
+  cudaError_t e = cudaSuccess;
+  unsigned char *base = nullptr;
+  if (pooled) {
+    if (bytes > c->pool_cap) {
+      if (c->d_pool) cudaFree(c->d_pool);
+      c->d_pool = nullptr;
+      c->pool_cap = 0;
+      e = cudaMalloc((void **)&c->d_pool, bytes + bytes / 4);
+      if (e == cudaSuccess) c->pool_cap = bytes + bytes / 4;
+    }
+    base = c->d_pool;
+    p->pooled = true;
+  } else {
+    e = cudaMalloc((void **)&base, bytes);
+  }
+  if (e == cudaSuccess) {
+    p->d_block = base;
+    p->d_params = reinterpret_cast<PointParams *>(base);
+    p->d_groups = reinterpret_cast<int2 *>(base + o_groups);
+    p->d_status0 = reinterpret_cast<int *>(base + o_status);
+    e = cudaMemcpy(base, stage.data(), bytes, cudaMemcpyHostToDevice);
+  }
   if (e != cudaSuccess) {
     nusi_points_destroy(p);
     return fail(NUSI_E_CUDA, std::string("points upload: ") + cudaGetErrorString(e));
@@ -638,12 +669,16 @@ int nusi_points_create(nusi_ctx *c, int n, const double *mphi, const double *g, 
   *out = p;
   return NUSI_OK;
 }
+int nusi_points_create(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
+                       nusi_points **out) {
+  return points_create_impl(c, n, mphi, g, mntot, out, false);
+}
 void nusi_points_destroy(nusi_points *p) {
   if (!p) return;
-  cudaSetDevice(p->device);
-  if (p->d_params) cudaFree(p->d_params);
-  if (p->d_status0) cudaFree(p->d_status0);
-  if (p->d_groups) cudaFree(p->d_groups);
+  if (!p->pooled && p->d_block) {
+    cudaSetDevice(p->device);
+    cudaFree(p->d_block);
+  }
   delete p;
 }
 int nusi_points_count(const nusi_points *p) { return p ? p->n : 0; }
@@ -793,7 +828,7 @@ int nusi_evolve_batch(nusi_ctx *c, int n, const double *mphi, const double *g, c
   int rc = ensure_streams(c);
   if (rc) return rc;
   nusi_points *p = nullptr;
-  if ((rc = nusi_points_create(c, n, mphi, g, mntot, &p))) return rc;
+  if ((rc = points_create_impl(c, n, mphi, g, mntot, &p, true))) return rc;
   cudaStream_t s = c->s_copy;  // any stream of ours serves as the "caller" of the pipeline
   cudaError_t e = cudaMemcpyAsync(c->d_out_st, p->d_status0, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, s);
   if (e == cudaSuccess)
