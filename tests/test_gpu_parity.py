@@ -327,6 +327,30 @@ def test_scan_builder_equals_compact_builder_bitwise(nusi):
     c2.close(); c3.close()
 
 
+def test_scan_builder_race_stress(nusi):
+    """compute-sanitizer is not available on the GPU pool, so the pipelined shared-memory hand-offs of the scan kernels
+    (double-buffered G, triple-buffered cp.async fields, one barrier per point) are stressed instead: a full 2048-point
+    slice plus a ragged tail, every group length 1..32 cut by NUSI_GROUP_MAX, repeated, each run compared bit for bit
+    with the compact builder (which has no per-point pipeline)."""
+    M, Gg = np.meshgrid(10 ** np.linspace(1, 4, 75), 10 ** np.linspace(-5, 0, 33), indexing="ij")
+    mphi, g = M.ravel(), Gg.ravel()
+    c2 = nusi.Context(elementary_mode=2, **CFG200)
+    ref = c2.evolve(mphi, g, 0.1)
+    c2.close()
+    c3 = nusi.Context(elementary_mode=3, **CFG200)
+    try:
+        for gm in (32, 2, 3, 5, 7, 11, 16, 31, 32, 32):
+            os.environ["NUSI_GROUP_MAX"] = str(gm)
+            os.environ["NUSI_GROUP_ALWAYS"] = "1"
+            got = c3.evolve(mphi, g, 0.1)
+            for a, b in zip(ref, got):
+                assert np.array_equal(a, b, equal_nan=True), gm
+    finally:
+        os.environ.pop("NUSI_GROUP_MAX", None)
+        os.environ.pop("NUSI_GROUP_ALWAYS", None)
+        c3.close()
+
+
 def test_batch_invariance_and_permutation(nusi):
     """A point's result does not depend on its batch: full scan shard vs singles vs permuted."""
     mphi, g = _scan_sample(300, 11)
