@@ -40,6 +40,9 @@ static cudaError_t upload(const std::vector<T> &h, T **d) {
 #ifndef NUSI_SLICE
 #define NUSI_SLICE 2048  // points per slice of the evolve pipeline (run_pipeline)
 #endif
+#ifndef NUSI_DIAG_SB_SMALL
+#define NUSI_DIAG_SB_SMALL 32  // z-steps per band of the integrator for N_bins_E <= 225
+#endif
 #define NUSI_GROUP_CAP 256  // most points of one scan-builder group
 
 struct nusi_ctx {
@@ -572,7 +575,7 @@ static int launch_integrate(nusi_ctx *c, const PointParams *d_params, int cnt, d
       const char *fv = getenv("NUSI_FINE_VARIANT");
       const bool wide = !(fv && atoi(fv) == 0);
       if (N <= 225 && NT <= 256 * 3)
-        NUSI_DIAG(1, 32, 1, 8);
+        NUSI_DIAG(1, NUSI_DIAG_SB_SMALL, 1, 8);
       else if (N <= 256 && NT <= 256 * 3)
         NUSI_DIAG(1, 32, 2, 8);
       else if (wide && N + 32 - 1 <= 512 && NT <= 512 * 3)
