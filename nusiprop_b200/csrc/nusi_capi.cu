@@ -574,7 +574,11 @@ static int launch_integrate(nusi_ctx *c, const PointParams *d_params, int cnt, d
   } while (0)
       const char *fv = getenv("NUSI_FINE_VARIANT");
       const bool wide = !(fv && atoi(fv) == 0);
-      if (N <= 225 && NT <= 256 * 3)
+      if (N <= 225 && NT <= 256 && !getenv("NUSI_DIAG_PRE3")) {  // a table column fits one row per thread (N_E = 200: NT = 231)
+        const size_t sh = (size_t)((8 + 2) * NT + 2 * NUSI_DIAG_SB_SMALL + 2 * NUSI_DIAG_SB_SMALL * NUSI_PRE_DOUBLES + 2 * S + 2 * N + 2) * sizeof(double);
+        CU(cudaFuncSetAttribute(integrate_diag_kernel<1, NUSI_DIAG_SB_SMALL, 1, 8, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+        integrate_diag_kernel<1, NUSI_DIAG_SB_SMALL, 1, 8, 256, 1><<<cnt, 256, sh, s>>>(G, d_params, W.rows, W.tri, c->tstride, d_fm, d_ff);
+      } else if (N <= 225 && NT <= 256 * 3)
         NUSI_DIAG(1, NUSI_DIAG_SB_SMALL, 1, 8);
       else if (N <= 256 && NT <= 256 * 3)
         NUSI_DIAG(1, 32, 2, 8);

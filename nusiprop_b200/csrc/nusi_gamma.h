@@ -217,7 +217,10 @@ NUSI_HD int gamma_mass_point(const PointParams &P, int j, const GammaShared &S, 
           (sqr(splus) * ((-I) / im + c2)) / 2.;
   } else {
     dd1 = dilogdiff_complex(z1p, z1m);
-    dd2 = dilogdiff_complex(z2p, z2m);
+    // z2 = conj(z1): every operation of dilogdiff_complex is sign-symmetric in the imaginary part (odd atan2, the
+    // sgn(Im z) continuation term), so Li2(conj z) comes out as the exact conjugate -- except on the real axis, where
+    // the GSL convention (Im = -pi ln x for x >= 1) is not conjugation-symmetric: evaluated there as written.
+    dd2 = (z1p.im != 0.0 && z1m.im != 0.0) ? conj(dd1) : dilogdiff_complex(z2p, z2m);
   }
   const double lam_p = nlog1p(sqr(-1 + splus) / sqr(gr)), lam_m = nlog1p(sqr(-1 + sminus) / sqr(gr));
   double Gst = -g4 / (32 * kPi * sqr(mphi) * (1 + sqr(gr))) *
