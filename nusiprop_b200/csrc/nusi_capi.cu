@@ -477,7 +477,14 @@ static int launch_rows(nusi_ctx *c, const PointParams *d_params, int cnt, int *d
   const int mode = mode_env ? atoi(mode_env) : c->opt.elementary_mode;
   if (mode >= 3 && d_groups && ngroups > 0 && G.majorana && G.non_resonant && !G.phiphi && !getenv("NUSI_ROWS_UNGROUPED")) {
     const char *rs = getenv("NUSI_ROWS_SPLIT");
-    dim3 gg(gr.x, ngroups, rs && atoi(rs) > 0 ? atoi(rs) : 4);  // scan: the g-independent part of a row once per (part of a) group
+    // scan: the g-independent part of a row once per (part of a) group.  A group is shared by `split` CTAs: 4 when the
+    // launch is large (the per-point part dominates, so repeating the shared part four times is cheap and the grid is
+    // 4x finer), more for small launches so that the grid still fills the 148 SMs x 4 CTAs twice (each CTA keeps >= 1 point).
+    int split = 4;
+    const long long want = 1184, have = (long long)gr.x * ngroups * split;
+    if (have < want) split = (int)std::min<long long>(32, (want + (long long)gr.x * ngroups - 1) / ((long long)gr.x * ngroups));
+    if (rs && atoi(rs) > 0) split = atoi(rs);
+    dim3 gg(gr.x, ngroups, split);
     rows_group_kernel<0><<<gg, NUSI_ROWS_PER_CTA * 3, 0, s>>>(G, d_params, d_groups, W.rows, d_status);
     rows_group_kernel<1><<<gg, NUSI_ROWS_PER_CTA * 3, 0, s>>>(G, d_params, d_groups, W.rows, d_status);
     c->n_launches += 2;
