@@ -5,10 +5,11 @@
  * header-only C++ class nuSIprop::calculate_flux (reference nuSIprop.hpp:22-540) and the Cython
  * wrapper pyprop (reference nuSIprop.pyx:12-144).  Each entry point below names the reference
  * interface it replaces; the drop-in class in nusiprop_b200/cxx/nuSIprop.hpp and the Python
- * mirror in nusiprop_b200/pyprop.py are thin callers of this ABI.
+ * mirror nusiprop_b200.pyprop (nusiprop_b200/api.py) are thin callers of this ABI.
  *
- * Threading: calls on ONE context must be serialised by the caller; distinct contexts are
- * independent.  All functions return NUSI_OK (0) or a negative NUSI_E_* code;
+ * Threading: every call that uses a context takes that context's own lock, so concurrent calls on ONE
+ * context are serialised by the library (objects of the drop-in class share contexts); distinct contexts
+ * are independent.  All functions return NUSI_OK (0) or a negative NUSI_E_* code;
  * nusi_strerror() maps codes to text.  There is no CPU compute path: without a CUDA device
  * nusi_ctx_create fails with NUSI_E_NO_DEVICE.
  */
@@ -19,7 +20,7 @@
 extern "C" {
 #endif
 
-#define NUSI_ABI_VERSION 2
+#define NUSI_ABI_VERSION 3
 
 /* error codes (function return values) */
 #define NUSI_OK 0
@@ -35,6 +36,7 @@ extern "C" {
 #define NUSI_ST_WARN_ALPHA 4      /* ... alpha                                                          nuSIprop.hpp:1505 */
 #define NUSI_ST_PP_RANGE 8        /* phi-phi lookup outside the table (reference: exit(1))              interp.hpp:355-361 */
 #define NUSI_ST_NO_MASS 256       /* no neutrino mass spectrum for this mntot (reference: exit(1))      aux.hpp:48-49 */
+#define NUSI_ST_BAD_PARAM 512     /* mphi <= 0, or a non-finite mphi / g / mntot: the point is not evolved, its fluxes are NaN */
 
 typedef struct nusi_ctx nusi_ctx;       /* one (device, option set): grids, source term, tables */
 typedef struct nusi_points nusi_points; /* a batch of prepared parameter points resident in HBM */
@@ -75,6 +77,25 @@ typedef struct nusi_opts {
   double si;             /* spectral index, source_model 1 only (default 2; si == 1 is rejected: the bin integral of
                             :656 divides by 1 - si) */
   double norm;           /* free-streaming flux at Earth at E0, source_model 1 only (default 1) */
+  /* ---- switches of the implementation (ABI 3; all default 0 = the product path).  They select cross-check
+   *      kernels and tuning variants that produce the same numbers; tests and tools set them here, nothing in the
+   *      library reads the environment. */
+  int integrator;        /* 0 = diagonal-owned wavefront kernel; 1 = bin-owned wavefront kernel (cross-check);
+                            2 = serial, reference-shaped bin-by-bin kernel with true divisions (cross-check, N_bins_E <= 256) */
+  int fine_variant;      /* 0 = 512 threads per point for N_bins_E > 256; 1 = the 256-thread configurations (same bits) */
+  int builder_per_entry; /* 1 = no tiling: one thread per table entry (cross-check of the tiled builders) */
+  int group_max;         /* most points per scan-builder group; 0 = 32 */
+  int group_always;      /* 1 = use the scan builder however short the groups are */
+  int rows_split;        /* CTAs that share one group in the row kernels; 0 = chosen from the launch size */
+  int rows_ungrouped;    /* 1 = per-point row kernels even on a scan */
+  int keep_order;        /* 1 = do not reorder a batch: by default the points are sorted by (mphi, mntot) before the
+                                groups are cut, so the scan builder's gain does not depend on the caller's order;
+                                results always come back in the caller's order */
+  int two_stream;        /* 1 = builder and rows + integrator on two streams (measured neutral on B200) */
+  int source_device;     /* source_model 0: 0 = Lum(z_i, bin j) computed on the host (same glibc calls as the reference,
+                                bit-identical to it) and uploaded; 1 = computed by the CUDA source kernel (device exp / log
+                                + Li2 / Li3; differs from the host array by up to 1e-6 in the four lowest bins, where the
+                                difference of antiderivatives cancels) */
 } nusi_opts;
 
 /* Fills *o with the reference's C++ constructor defaults (nuSIprop.hpp:61-65). */
@@ -97,8 +118,12 @@ int nusi_ctx_energies(const nusi_ctx *c, double *Emin, double *Ecen, double *Ema
 int nusi_ctx_redshifts(const nusi_ctx *c, double *z);
 /* |U_ab|^2, [3][3] row-major, a = flavour, b = mass (nuSIprop.hpp:155-163, used as std::norm). */
 int nusi_ctx_pmns2(const nusi_ctx *c, double *U2);
-/* The device-computed source term: out[(i-1)*N + j] = Lum(z[i], Emin[j], Emax[j]), i = 1..N_steps_z-1. */
+/* The source term resident in HBM: out[(i-1)*N + j] = Lum(z[i], Emin[j], Emax[j]), i = 1..N_steps_z-1
+ * (nuSIprop.hpp:659-662; per mass eigenstate). */
 int nusi_ctx_source(const nusi_ctx *c, double *out);
+/* source_model 1 only: replace the power-law source of the context by the one for (si, norm) -- the public members
+ * calculate_flux re-reads at each evolve() (nuSIprop.hpp:174, :205) -- without creating a new context. */
+int nusi_ctx_set_powerlaw(nusi_ctx *c, double si, double norm);
 
 /* The same grids WITHOUT a context or a GPU (host arithmetic only): what the constructor of
  * calculate_flux computes at nuSIprop.hpp:113-128.  Emin/Ecen/Emax are [N_bins_E] or NULL; the
@@ -111,6 +136,20 @@ int nusi_grid(int N_bins_E, double lEmin, double lEmax, double zmax, int *N_step
  * check_energy_conservation() (:339-357) compares the evolved flux with.  Host arithmetic
  * (300 pow() calls); zmax_eff is the context's effective zmax (z[N_steps_z-1]). */
 int nusi_freestream_energy(double zmax_eff, double lEmin, double lEmax, double si, double norm, double *E_FS);
+
+/* Free-streaming energy of the context's OWN source, the counterpart of energy_FS() (nuSIprop.hpp:694-729) for it:
+ *     E_FS = \int_0^zmax dz/H(z) \int_Emin^Emax dE E sum_i L^i(z, E (1+z))
+ * source_model 0 (this fork's diffuse supernova background, L^i = R_SN(z) dN/dE(E (1+z)), :607-662): the z integral by the
+ * reference's 100 x 3 Gauss-Legendre panels, the E integral by Gauss-Legendre panels in ln E (the reference has no
+ * closed form for it: it compares the supernova-sourced flux with the POWER-LAW energy, SURVEY 0.2, so its
+ * check_energy_conservation() returns -1 in the fork's default mode).  source_model 1: nusi_freestream_energy() for the
+ * context's (si, norm).  Host arithmetic.  With this E_FS, (E_int - E_FS)/E_FS is what check_energy_conservation() is
+ * meant to be: the discretisation error in the free-streaming limit, the energy the interactions fail to conserve otherwise. */
+int nusi_ctx_freestream_energy(nusi_ctx *c, double *E_FS);
+/* E_int of check_energy_conservation() (nuSIprop.hpp:351-355) for n points whose mass-basis fluxes are in HBM
+ * (d_flux_mass [n][3][N], as nusi_evolve_points leaves them): a device reduction, one double per point into the
+ * HOST array E_int[n]. */
+int nusi_energy_integral(nusi_ctx *c, int n, const double *d_flux_mass, double *E_int, void *stream);
 
 /* Bin-integrated power-law source of nusi_opts.source_model == 1 -- the upstream Lum() that the reference keeps as a
  * comment (nuSIprop.hpp:648-657) with norm_total = norm / flux_FS_E0() (:205, :666-692) -- for the grids of
@@ -161,6 +200,10 @@ int nusi_tables_batch(nusi_ctx *c, int n, const double *mphi, const double *g, c
  * path may be NULL to skip that table.  seconds (may be NULL) receives the CUDA-event time of the kernels. */
 int nusi_phiphi_tables_generate(int device, const char *alphatilde_path, const char *alpha_path, int n_t, int n_s,
                                 int n_n, int n_d, double *seconds);
+
+/* How the last batch prepared on this context (nusi_points_create / nusi_evolve_batch) was laid out for the scan
+ * builder: number of groups, points in groups of more than one point, and whether the batch had to be reordered. */
+int nusi_last_grouping(const nusi_ctx *c, int *n_groups, int *n_grouped_points, int *reordered);
 
 /* CUDA-event time of the last nusi_evolve_points / nusi_evolve_batch on this context, per kernel,
  * summed over its launches [ms]: Gamma/alphaTilde rows, alpha table, z-stepping integrator; and

@@ -31,7 +31,22 @@ class NusiOpts(C.Structure):
         ("source_model", C.c_int),
         ("si", C.c_double),
         ("norm", C.c_double),
+        # implementation switches (ABI 3): cross-check kernels and tuning variants, all default 0
+        ("integrator", C.c_int),
+        ("fine_variant", C.c_int),
+        ("builder_per_entry", C.c_int),
+        ("group_max", C.c_int),
+        ("group_always", C.c_int),
+        ("rows_split", C.c_int),
+        ("rows_ungrouped", C.c_int),
+        ("keep_order", C.c_int),
+        ("two_stream", C.c_int),
+        ("source_device", C.c_int),
     ]
+
+
+SWITCHES = ("integrator", "fine_variant", "builder_per_entry", "group_max", "group_always", "rows_split", "rows_ungrouped", "keep_order",
+            "two_stream", "source_device")
 
 
 # name -> (restype, argtypes); also the list tests check against the header
@@ -47,6 +62,10 @@ SIGNATURES = {
     "nusi_ctx_redshifts": (C.c_int, [C.c_void_p, c_double_p]),
     "nusi_ctx_pmns2": (C.c_int, [C.c_void_p, c_double_p]),
     "nusi_ctx_source": (C.c_int, [C.c_void_p, c_double_p]),
+    "nusi_ctx_set_powerlaw": (C.c_int, [C.c_void_p, C.c_double, C.c_double]),
+    "nusi_ctx_freestream_energy": (C.c_int, [C.c_void_p, c_double_p]),
+    "nusi_energy_integral": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, c_double_p, C.c_void_p]),
+    "nusi_last_grouping": (C.c_int, [C.c_void_p, c_int_p, c_int_p, c_int_p]),
     "nusi_grid": (C.c_int, [C.c_int, C.c_double, C.c_double, C.c_double, c_int_p, c_double_p, c_double_p, c_double_p, c_double_p]),
     "nusi_freestream_energy": (C.c_int, [C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, c_double_p]),
     "nusi_powerlaw_source": (C.c_int, [C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, c_double_p]),

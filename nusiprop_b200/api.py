@@ -31,7 +31,9 @@ class Context(object):
 
     def __init__(self, majorana=True, non_resonant=True, normal_ordering=True, N_bins_E=300, lEmin=12.0,
                  lEmax=17.0, zmax=5.0, flav=2, phiphi=False, device=0, alphatilde_phiphi_path=None,
-                 alpha_phiphi_path=None, max_points_per_launch=0, elementary_mode=None, source_model=0, si=2.0, norm=1.0):
+                 alpha_phiphi_path=None, max_points_per_launch=0, elementary_mode=None, source_model=0, si=2.0, norm=1.0, **switches):
+        """switches: the implementation switches of nusi_opts (integrator, fine_variant, builder_per_entry, group_max,
+        group_always, rows_split, rows_ungrouped, keep_order, two_stream, source_device); all default 0."""
         self._lib = _lib.load()
         o = NusiOpts()
         check(self._lib.nusi_opts_default(C.byref(o)), "nusi_opts_default")
@@ -43,6 +45,10 @@ class Context(object):
             o.elementary_mode = int(elementary_mode)
         # 0: the reference's DSNB source; 1: upstream power law norm * (E/1e14 eV)^-si at Earth (nuSIprop.hpp:648-657)
         o.source_model, o.si, o.norm = int(source_model), float(si), float(norm)
+        for k, v in switches.items():
+            if k not in _lib.SWITCHES:
+                raise TypeError("Context() got an unexpected keyword argument %r" % k)
+            setattr(o, k, int(v))
         self._paths = (
             alphatilde_phiphi_path.encode() if alphatilde_phiphi_path else None,
             alpha_phiphi_path.encode() if alpha_phiphi_path else None,
@@ -129,6 +135,28 @@ class Context(object):
         check(self._lib.nusi_evolve_points(self._h, pts._h, C.c_void_p(d_flux_mass or None), C.c_void_p(d_flux_fla or None),
                                            C.c_void_p(d_status or None), C.c_void_p(stream or None)), "nusi_evolve_points")
 
+    def set_powerlaw(self, si, norm):
+        """source_model 1: replace the context's power-law source by the one for (si, norm)."""
+        check(self._lib.nusi_ctx_set_powerlaw(self._h, float(si), float(norm)), "nusi_ctx_set_powerlaw")
+
+    def freestream_energy(self):
+        """E_FS of the context's own source (DSNB for source_model 0, power law for 1): nusi_ctx_freestream_energy."""
+        e = C.c_double()
+        check(self._lib.nusi_ctx_freestream_energy(self._h, C.byref(e)), "nusi_ctx_freestream_energy")
+        return e.value
+
+    def energy_integral(self, d_flux_mass, n, stream=0):
+        """E_int of check_energy_conservation (nuSIprop.hpp:351-355) for n points whose mass-basis fluxes are in HBM at the
+        device address d_flux_mass ([n][3][N]); a device reduction, returns a host array [n]."""
+        out = np.zeros(int(n))
+        check(self._lib.nusi_energy_integral(self._h, int(n), C.c_void_p(d_flux_mass), _dp(out), C.c_void_p(stream or None)), "nusi_energy_integral")
+        return out
+
+    def last_grouping(self):
+        a, b, r = C.c_int(), C.c_int(), C.c_int()
+        check(self._lib.nusi_last_grouping(self._h, C.byref(a), C.byref(b), C.byref(r)))
+        return dict(n_groups=a.value, n_grouped_points=b.value, reordered=bool(r.value))
+
     def last_timing(self):
         r, a, b, n = C.c_float(), C.c_float(), C.c_float(), C.c_int()
         check(self._lib.nusi_last_timing(self._h, C.byref(r), C.byref(a), C.byref(b), C.byref(n)))
@@ -214,7 +242,8 @@ class pyprop(object):
     shared between objects with identical fixed options.
     """
 
-    _ctx_cache = {}
+    _ctx_cache = {}      # fixed options -> Context, at most _CTX_CACHE_MAX of them (least recently used closed first)
+    _CTX_CACHE_MAX = 8
 
     def __init__(self, mphi, g, mntot, si, norm=1, majorana=True, non_resonant=True, normal_ordering=True,
                  N_bins_E=300, lEmin=12.0, lEmax=17.0, zmax=5.0, flav=2, phiphi=True, device=0, source_model=0):
@@ -232,16 +261,20 @@ class pyprop(object):
         self.status = 0
 
     def _acquire(self):
-        """Context for the fixed options (+ si, norm when they define the source); shared between objects."""
-        extra = (self.si, self.norm) if self._fixed["source_model"] == 1 else ()
-        key = tuple(sorted(self._fixed.items())) + extra
-        ctx = pyprop._ctx_cache.get(key)
-        if ctx is None:
+        """Context for the fixed options, shared between objects.  si and norm are NOT part of the key: with
+        source_model 1 evolve() re-uploads the power-law table of the shared context when they differ, so sampling
+        si never creates contexts."""
+        key = tuple(sorted(self._fixed.items()))
+        cache = pyprop._ctx_cache
+        ctx = cache.pop(key, None)
+        if ctx is None or ctx._h is None:
             kw = dict(self._fixed)
-            if extra:
+            if self._fixed["source_model"] == 1:
                 kw.update(si=self.si, norm=self.norm)
             ctx = Context(**kw)
-            pyprop._ctx_cache[key] = ctx
+        cache[key] = ctx  # most recently used last
+        while len(cache) > pyprop._CTX_CACHE_MAX:
+            cache.pop(next(iter(cache))).close()  # objects that still hold it re-acquire at their next use
         return ctx
 
     def set_parameters(self, mphi=None, g=None, mntot=None, si=None, norm=None):
@@ -262,6 +295,8 @@ class pyprop(object):
         """Evolve the neutrino flux (reference nuSIprop.pyx:87-90)."""
         self.evolved = True
         self._ctx = self._acquire()
+        if self._fixed["source_model"] == 1:
+            self._ctx.set_powerlaw(self.si, self.norm)
         fm, ff, st = self._ctx.evolve(self.mphi, self.g, self.mntot)
         self.status = int(st[0])
         if self.status & 256:
@@ -299,6 +334,7 @@ class pyprop(object):
 
     def get_energies(self):
         """Energy bin centers (reference nuSIprop.pyx:130-138)."""
+        self._ctx = self._acquire()
         return self._ctx.energies()[1].copy()
 
     def check_energy_conservation(self):
@@ -312,4 +348,19 @@ class pyprop(object):
         for i in range(self._ctx.N_bins_E):
             for k in range(3):
                 E_int += (np.log(Emax[i]) - np.log(Emin[i])) * Ecen[i] ** 2 * self._flux[k][i]
+        return (E_int - E_FS) / E_FS
+
+    def check_energy_conservation_consistent(self):
+        """(E_int - E_FS)/E_FS with E_FS the free-streaming energy of the source that is actually injected (the
+        supernova background for source_model 0): what check_energy_conservation() is meant to measure.  E_int is the
+        device reduction nusi_energy_integral over the fluxes in HBM.  Extra; not in the reference."""
+        import torch
+        self._ctx = self._acquire()
+        if self._fixed["source_model"] == 1:
+            self._ctx.set_powerlaw(self.si, self.norm)
+        E_FS = self._ctx.freestream_energy()
+        self.evolve()
+        dev = torch.device("cuda", self._ctx.device)
+        fm = torch.as_tensor(self._flux, device=dev).contiguous()
+        E_int = self._ctx.energy_integral(fm.data_ptr(), 1)[0]
         return (E_int - E_FS) / E_FS

@@ -7,38 +7,63 @@ import sys
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 OUT = os.path.join(_HERE, "lib", "libnusiprop_b200.so")
-SOURCES = ["nusi_capi.cu", "nusi_host.cpp"]
+# Kernel translation units: they are independent of each other, so they compile in parallel.
+SOURCES = ["nusi_capi.cu", "k_rows.cu", "k_alpha.cu", "k_alpha_check.cu", "k_integrate.cu", "k_integrate_check.cu", "k_misc.cu", "k_phiphi.cu",
+           "nusi_host.cpp"]
+OBJ_DIR = os.path.join(_HERE, "lib", "build")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
     # no implicit contraction: the closed forms must round as written (explicit fma() only)
     "-fmad=false",
     "-Xcompiler", "-fPIC,-ffp-contract=off",
-    "-shared",
 ]
 
 
-def _stale():
-    if not os.path.exists(OUT):
-        return True
-    t = os.path.getmtime(OUT)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
-    deps.append(os.path.join(_HERE, "..", "include", "nusiprop_b200.h"))
-    deps.append(os.path.abspath(__file__))
-    return any(os.path.getmtime(d) > t for d in deps)
+def _deps(path, seen=None):
+    """The file and every header it includes (transitively, quoted includes only)."""
+    import re
+    seen = set() if seen is None else seen
+    path = os.path.normpath(path)
+    if path in seen or not os.path.exists(path):
+        return seen
+    seen.add(path)
+    for inc in re.findall(r'^\s*#\s*include\s+"([^"]+)"', open(path).read(), re.M):
+        _deps(os.path.join(os.path.dirname(path), inc), seen)
+    return seen
 
 
-def build_library(force=False, verbose=False):
-    if not force and not _stale():
-        return OUT
-    os.makedirs(os.path.dirname(OUT), exist_ok=True)
+def build_library(force=False, verbose=False, extra_flags=(), out=None):
+    """Compile every translation unit whose object is older than its source or any header, then link.
+    extra_flags / out: alternative builds of the same sources (tests: -DNUSI_LOCKED_LIBM; tuning experiments)."""
+    out = out or OUT
+    obj_dir = OBJ_DIR if out == OUT else os.path.join(os.path.dirname(out), "build_" + os.path.basename(out))
+    os.makedirs(obj_dir, exist_ok=True)
     nvcc = os.environ.get("NVCC", "nvcc")
-    cmd = [nvcc] + FLAGS + ["-o", OUT] + [os.path.join(CSRC, s) for s in SOURCES]
-    if verbose:
-        cmd += ["-Xptxas", "-v"]
-        print(" ".join(cmd), file=sys.stderr)
-    subprocess.check_call(cmd)
-    return OUT
+    self_t = os.path.getmtime(os.path.abspath(__file__))
+    jobs, objs = [], []
+    for src in SOURCES:
+        sp = os.path.join(CSRC, src)
+        ob = os.path.join(obj_dir, os.path.splitext(src)[0] + ".o")
+        objs.append(ob)
+        if force or not os.path.exists(ob) or os.path.getmtime(ob) < max([self_t] + [os.path.getmtime(d) for d in _deps(sp)]):
+            cmd = [nvcc] + FLAGS + list(extra_flags) + ["-c", "-o", ob, sp]
+            if verbose:
+                cmd += ["-Xptxas", "-v"]
+                print(" ".join(cmd), file=sys.stderr)
+            jobs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    failed = []
+    for src, pr in jobs:
+        log = pr.communicate()[0]
+        if verbose or pr.returncode != 0:
+            sys.stderr.write(log)
+        if pr.returncode != 0:
+            failed.append(src)
+    if failed:
+        raise RuntimeError("nvcc failed for: " + ", ".join(failed))
+    if jobs or not os.path.exists(out):
+        subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", out] + objs)
+    return out
 
 
 ROOT = os.path.dirname(_HERE)

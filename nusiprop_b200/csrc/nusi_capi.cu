@@ -1,20 +1,25 @@
-// nusi_capi.cu -- implementation of include/nusiprop_b200.h: contexts, batches of points, and the
-// launch sequence  rows_kernel + alpha_kernel (cross-section builder)  ->  integrate_kernel.
-// There is deliberately no host compute path in this library.
+// nusi_capi.cu -- implementation of include/nusiprop_b200.h: contexts, batches of points, and the evolve pipeline
+//     rows kernels + edges + alpha table builder  ->  z-stepping integrator (epilogue fused).
+// The kernels live in k_*.cu and are reached through nusi_launch.h.  There is deliberately no host compute path
+// in this library; nothing here reads the environment (every switch is a field of nusi_opts).
 #include "../../include/nusiprop_b200.h"
-#include "nusi_kernels.cuh"
+#include "nusi_launch.h"
 #include "nusi_host.hpp"
 
 #include <cuda_runtime.h>
+#include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <algorithm>
 #include <array>
-#include <map>
+#include <mutex>
+#include <numeric>
 #include <string>
-#include <vector>
+#include <unordered_map>
 #include <utility>
+#include <vector>
 
 using namespace nusi;
 
@@ -27,7 +32,8 @@ static int fail(int code, const std::string &msg) {
   do {                                                                                             \
     cudaError_t e_ = (call);                                                                       \
     if (e_ != cudaSuccess)                                                                         \
-      return fail(NUSI_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));                \
+      return fail(e_ == cudaErrorMemoryAllocation ? NUSI_E_NOMEM : NUSI_E_CUDA,                    \
+                  std::string(#call) + ": " + cudaGetErrorString(e_));                             \
   } while (0)
 
 template <typename T>
@@ -40,61 +46,68 @@ static cudaError_t upload(const std::vector<T> &h, T **d) {
 #ifndef NUSI_SLICE
 #define NUSI_SLICE 2048  // points per slice of the evolve pipeline (run_pipeline)
 #endif
-#ifndef NUSI_DIAG_SB_SMALL
-#define NUSI_DIAG_SB_SMALL 32  // z-steps per band of the integrator for N_bins_E <= 225
-#endif
-#define NUSI_GROUP_CAP 256  // most points of one scan-builder group
+#define NUSI_GROUP_CAP 256       // most points of one scan-builder group
+#define NUSI_MASS_CACHE_MAX 4096  // distinct mass sums memoised per context
 
 struct nusi_ctx {
+  std::mutex mu;  // every entry point that uses the context holds it
   nusi_opts opt;
+  std::string path_at, path_a;  // own copies of the table paths (opt's pointers belong to the caller)
   HostGrid H;
   DeviceGrid G;
   // device arrays owned by the context
   double *d_row_lo = nullptr, *d_row_hi = nullptr, *d_dE = nullptr, *d_cz = nullptr, *d_ndz = nullptr;
-  double *d_source = nullptr, *d_Emin = nullptr, *d_Emax = nullptr, *d_zsrc = nullptr, *d_rsn = nullptr;
+  double *d_source = nullptr, *d_Emin = nullptr, *d_Emax = nullptr, *d_zsrc = nullptr, *d_rsn = nullptr, *d_wE2 = nullptr;
   double *d_pp[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-  double *d_edgeE = nullptr;  // distinct bin-edge energies of the table cells (tiled builder)
+  double *d_edgeE = nullptr;  // distinct bin-edge energies of the table cells (tiled builders)
   int2 *d_tiles = nullptr;
   int n_tiles = 0;
   unsigned char *d_pool = nullptr;  // points block of nusi_evolve_batch, kept across calls
   size_t pool_cap = 0;
   int2 *d_unit_groups = nullptr;  // (0, L) for L = 0..NUSI_GROUP_CAP: one-group launches of the scan builder
-  int4 *d_ctiles = nullptr;  // compact builder: per tile the cell ranges [a0, a1) x [b0, b1) of its row / column segment
+  int4 *d_ctiles = nullptr;       // compact builder: per tile the cell ranges [a0, a1) x [b0, b1) of its row / column segment
   int n_ctiles = 0;
   int n_edges = 0;
   bool use_tiles = false;
-  double *d_edges = nullptr;  // per-launch edge blocks [cap_points][edge_block_doubles]
-  // per-launch work space (grown on demand)
+  // per-launch work space (grown on demand): slot i of rows / tri / edges / work / stat belongs to point i of a chunk
   int cap_points = 0;
   size_t tstride = 0;
-  double *d_rows = nullptr, *d_tri = nullptr, *d_work = nullptr;
+  double *d_rows = nullptr, *d_tri = nullptr, *d_work = nullptr, *d_edges = nullptr;
   int max_chunk = 0;
-  // host-buffer path (nusi_evolve_batch): device staging of the outputs, a compute and a copy stream
-  double *d_out_fm = nullptr, *d_out_ff = nullptr;
+  // host-buffer path (nusi_evolve_batch): device staging of the outputs, page-locked host staging, streams
+  double *d_out_fm = nullptr, *d_out_ff = nullptr, *d_eint = nullptr;
   int *d_out_st = nullptr;
-  int out_cap = 0;
-  cudaStream_t s_x = nullptr, s_i = nullptr, s_copy = nullptr;  // builder, rows+integrator (high priority), D2H
+  int out_cap = 0, eint_cap = 0;
+  unsigned char *h_stage = nullptr;  // page-locked
+  size_t h_stage_cap = 0;
+  cudaStream_t s_main = nullptr, s_x = nullptr, s_i = nullptr, s_copy = nullptr;  // pipeline, builder, rows+integrator, D2H
   cudaEvent_t ev_fork = nullptr, ev_jx = nullptr, ev_ji = nullptr, ev_jc = nullptr;
-  std::vector<cudaEvent_t> ev_alpha, ev_done;  // per slice: table ready / fluxes ready
+  std::vector<cudaEvent_t> ev_alpha, ev_done, ev_copied;  // per slice: table ready / fluxes ready / fluxes on the host
   // timing of the last evolve call
   std::vector<cudaEvent_t> ev;  // per slice 6: rows begin/end, builder begin/end, integrator begin/end
   int ev_used = 0;
   int n_launches = 0;
-  std::map<std::pair<double, int>, std::pair<bool, std::array<double, 3>>> mass_cache;
+  int last_groups = 0, last_grouped_points = 0, last_reordered = 0;
+  std::unordered_map<uint64_t, std::pair<bool, std::array<double, 3>>> mass_cache;
 };
 
 struct nusi_points {
   int n = 0;
   int device = 0;
+  // Points in EVOLVE order: sorted by (mphi, mntot) unless opts.keep_order, so that the points of a scan row are
+  // neighbours whatever order the caller used.  out_index[i] = the caller's index of evolve-order point i.
   PointParams *d_params = nullptr;
-  int *d_status0 = nullptr;  // host-side status (NO_MASS) pre-uploaded, OR'ed into the outputs
-  std::vector<int> h_status0;
-  // scan builder (elementary_mode 3): runs of consecutive points with identical (mphi, m_nu), cut at slice boundaries
-  // and at NUSI_GROUP_MAX points; (first point relative to its slice, length)
+  int *d_status0 = nullptr;   // host-side status (NO_MASS, BAD_PARAM), evolve order
+  int *d_statw = nullptr;     // working copy the builder kernels OR their warning bits into
+  int *d_out_index = nullptr; // NULL when the evolve order is the caller's order
+  bool reordered = false;
+  // scan builder: runs of consecutive points with identical (mphi, m_nu), cut at slice boundaries and at
+  // group_max points; (first point relative to its slice, length)
   int2 *d_groups = nullptr;
-  unsigned char *d_block = nullptr;  // the one device allocation behind d_params / d_groups / d_status0
+  unsigned char *d_block = nullptr;  // the one device allocation behind the arrays above
   bool pooled = false;               // d_block belongs to the context (nusi_evolve_batch)
-  std::vector<int2> h_groups;  // host copy with ABSOLUTE first point (nusi_tables_batch)
+  std::vector<int2> h_groups;  // host copy with ABSOLUTE first point (evolve order)
+  std::vector<int> h_out_index;
   std::vector<int> slice_g0;  // slice k owns groups [slice_g0[k], slice_g0[k+1])
   int SL = 0;                 // the slice length the groups were cut for
 };
@@ -136,34 +149,60 @@ int nusi_opts_default(nusi_opts *o) {
 }
 
 int nusi_masses(double mntot, int normal_ordering, double mn[3]) {
-  if (!mn) return NUSI_E_INVALID;
+  if (!mn || !std::isfinite(mntot)) return NUSI_E_INVALID;
   return solve_masses(mntot, normal_ordering != 0, mn) ? NUSI_OK : NUSI_E_INVALID;
+}
+
+static void free_workspace(nusi_ctx *c) {
+  for (double **p : {&c->d_rows, &c->d_tri, &c->d_work, &c->d_edges}) {
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+  }
+  c->cap_points = 0;
 }
 
 void nusi_ctx_destroy(nusi_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->opt.device);
-  double *ptrs[] = {c->d_row_lo, c->d_row_hi, c->d_dE, c->d_cz, c->d_ndz, c->d_source, c->d_Emin, c->d_Emax,
-                    c->d_zsrc, c->d_rsn, c->d_pp[0], c->d_pp[1], c->d_pp[2], c->d_pp[3], c->d_pp[4],
-                    c->d_rows, c->d_tri, c->d_work, c->d_edgeE, c->d_edges};
-  if (c->d_out_fm) cudaFree(c->d_out_fm);
-  if (c->d_out_ff) cudaFree(c->d_out_ff);
+  cudaDeviceSynchronize();
+  free_workspace(c);
+  double *ptrs[] = {c->d_row_lo, c->d_row_hi, c->d_dE, c->d_cz, c->d_ndz, c->d_source, c->d_Emin, c->d_Emax, c->d_zsrc,
+                    c->d_rsn, c->d_wE2, c->d_pp[0], c->d_pp[1], c->d_pp[2], c->d_pp[3], c->d_pp[4], c->d_edgeE,
+                    c->d_out_fm, c->d_out_ff, c->d_eint};
+  for (double *p : ptrs)
+    if (p) cudaFree(p);
   if (c->d_out_st) cudaFree(c->d_out_st);
-  if (c->s_x) cudaStreamDestroy(c->s_x);
-  if (c->s_i) cudaStreamDestroy(c->s_i);
-  if (c->s_copy) cudaStreamDestroy(c->s_copy);
-  for (cudaEvent_t e : c->ev_done) cudaEventDestroy(e);
-  for (cudaEvent_t e : c->ev_alpha) cudaEventDestroy(e);
+  if (c->h_stage) cudaFreeHost(c->h_stage);
+  for (cudaStream_t s : {c->s_main, c->s_x, c->s_i, c->s_copy})
+    if (s) cudaStreamDestroy(s);
+  for (auto *v : {&c->ev_done, &c->ev_alpha, &c->ev_copied, &c->ev})
+    for (cudaEvent_t e : *v) cudaEventDestroy(e);
   for (cudaEvent_t e : {c->ev_fork, c->ev_jx, c->ev_ji, c->ev_jc})
     if (e) cudaEventDestroy(e);
   if (c->d_tiles) cudaFree(c->d_tiles);
   if (c->d_ctiles) cudaFree(c->d_ctiles);
   if (c->d_unit_groups) cudaFree(c->d_unit_groups);
   if (c->d_pool) cudaFree(c->d_pool);
-  for (double *p : ptrs)
-    if (p) cudaFree(p);
-  for (cudaEvent_t e : c->ev) cudaEventDestroy(e);
   delete c;
+}
+
+// source term of the context (nuSIprop.hpp:638-662 or the power law of :648-657) -> c->d_source
+static int upload_source(nusi_ctx *c) {
+  const HostGrid &H = c->H;
+  const int S = H.Nz - 1;
+  if (!c->d_source) CU(cudaMalloc((void **)&c->d_source, (size_t)S * H.N * sizeof(double)));
+  if (c->opt.source_model == 1 || !c->opt.source_device) {
+    std::vector<double> src((size_t)S * H.N);
+    if (c->opt.source_model == 1)
+      powerlaw_source(H.N, S, H.zsrc.data(), H.Emin.data(), H.Emax.data(), H.zmax_eff, c->opt.si, c->opt.norm, src.data());
+    else  // the reference's own arithmetic with the same glibc calls: bit-identical to its Lum()
+      dsnb_source(H.N, S, H.zsrc.data(), H.rsn.data(), H.lum_pref, H.Emin.data(), H.Emax.data(), src.data());
+    CU(cudaMemcpy(c->d_source, src.data(), src.size() * sizeof(double), cudaMemcpyHostToDevice));
+  } else {
+    CU(launch_source(H.N, S, c->d_zsrc, c->d_rsn, H.lum_pref, c->d_Emin, c->d_Emax, c->d_source, nullptr));
+    CU(cudaDeviceSynchronize());
+  }
+  return NUSI_OK;
 }
 
 int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
@@ -174,6 +213,8 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
   if (o->source_model < 0 || o->source_model > 1 ||
       (o->source_model == 1 && (!(std::fabs(1 - o->si) > 1e-12) || !std::isfinite(o->si) || !std::isfinite(o->norm))))
     return fail(NUSI_E_INVALID, "bad source options (source_model 0 or 1; si != 1 and finite; norm finite)");
+  if (o->integrator < 0 || o->integrator > 2 || o->group_max < 0 || o->rows_split < 0 || o->elementary_mode < 0)
+    return fail(NUSI_E_INVALID, "bad implementation switches");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || o->device < 0 || o->device >= ndev)
     return fail(NUSI_E_NO_DEVICE, "no CUDA device with the requested ordinal");
@@ -181,11 +222,20 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
 
   nusi_ctx *c = new nusi_ctx;
   c->opt = *o;
+  if (o->alphatilde_phiphi_path) c->path_at = o->alphatilde_phiphi_path;
+  if (o->alpha_phiphi_path) c->path_a = o->alpha_phiphi_path;
+  c->opt.alphatilde_phiphi_path = c->opt.alpha_phiphi_path = nullptr;
   build_grid(o->N_bins_E, o->lEmin, o->lEmax, o->zmax, o->normal_ordering != 0, c->H);
   const HostGrid &H = c->H;
   if (H.Nz < 2) {
     delete c;
     return fail(NUSI_E_INVALID, "zmax too small for this binning (fewer than 2 redshift steps)");
+  }
+  // the integrators' limits are known now: say so here, not at the first evolve()
+  if (o->non_resonant && (!integrate_diag_supports(H.N, H.NT) || (o->integrator == 2 && H.N > 256))) {
+    delete c;
+    return fail(NUSI_E_INVALID, o->integrator == 2 ? "the serial cross-check integrator supports N_bins_E <= 256"
+                                                   : "binning not supported by the integrator (N_bins_E <= 2041, N_bins_E + N_steps_z - 2 <= 3072)");
   }
 #define UP(vec, ptr)                                                            \
   do {                                                                          \
@@ -204,6 +254,11 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
   UP(H.Emax, c->d_Emax);
   UP(H.zsrc, c->d_zsrc);
   UP(H.rsn, c->d_rsn);
+  {
+    std::vector<double> w(H.N);  // (ln Emax - ln Emin) E^2 of check_energy_conservation (nuSIprop.hpp:354)
+    for (int i = 0; i < H.N; ++i) w[i] = (std::log(H.Emax[i]) - std::log(H.Emin[i])) * sqr(H.Ecen[i]);
+    UP(w, c->d_wE2);
+  }
 
   DeviceGrid &G = c->G;
   std::memset(&G, 0, sizeof(G));
@@ -223,8 +278,8 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
 
   if (G.phiphi) {
     HostPhiPhi T;
-    const char *p_at = o->alphatilde_phiphi_path ? o->alphatilde_phiphi_path : "xsec/alphatilde_phiphi.bin";
-    const char *p_a = o->alpha_phiphi_path ? o->alpha_phiphi_path : "xsec/alpha_phiphi.bin";
+    const char *p_at = !c->path_at.empty() ? c->path_at.c_str() : "xsec/alphatilde_phiphi.bin";
+    const char *p_a = !c->path_a.empty() ? c->path_a.c_str() : "xsec/alpha_phiphi.bin";
     const std::string err = load_phiphi(p_at, p_a, std::log10(H.Emax[0] / H.Emin[0]), T);
     if (!err.empty()) {
       nusi_ctx_destroy(c);
@@ -247,28 +302,15 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
   }
 #undef UP
 
-  // source term, once per context, on the device
-  const int S = H.Nz - 1;
-  cudaError_t e = cudaMalloc((void **)&c->d_source, (size_t)S * H.N * sizeof(double));
-  if (e == cudaSuccess && o->source_model == 1) {
-    // upstream power law (nuSIprop.hpp:648-657): host arithmetic (glibc pow), uploaded once
-    std::vector<double> src((size_t)S * H.N);
-    powerlaw_source(H.N, S, H.zsrc.data(), H.Emin.data(), H.Emax.data(), H.zmax_eff, o->si, o->norm, src.data());
-    e = cudaMemcpy(c->d_source, src.data(), src.size() * sizeof(double), cudaMemcpyHostToDevice);
-  } else if (e == cudaSuccess) {
-    source_kernel<<<(S * H.N + 127) / 128, 128>>>(H.N, S, c->d_zsrc, c->d_rsn, H.lum_pref, c->d_Emin, c->d_Emax,
-                                                  c->d_source);
-    e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaDeviceSynchronize();
-  }
-  if (e != cudaSuccess) {
+  // source term, once per context
+  if (int rc = upload_source(c)) {
     nusi_ctx_destroy(c);
-    return fail(NUSI_E_CUDA, std::string("source_kernel: ") + cudaGetErrorString(e));
+    return rc;
   }
   G.source = c->d_source;
 
-  // tiled builder (Majorana + non-resonant): edge list with shared main-grid edges
-  if (G.non_resonant && G.majorana && !getenv("NUSI_NO_TILES")) {
+  // tiled builders (Majorana + non-resonant): edge list with shared main-grid edges
+  if (G.non_resonant && G.majorana && !o->builder_per_entry) {
     bool shared_ok = true;
     for (int a = 0; a + 1 < H.N; ++a) shared_ok = shared_ok && (H.row_hi[a] == H.row_lo[a + 1]);
     if (shared_ok) {
@@ -301,13 +343,8 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
       std::vector<int2> unit;
       for (int L = 0; L <= NUSI_GROUP_CAP; ++L) unit.push_back(make_int2(0, L));
       if (e1 == cudaSuccess) e1 = upload(unit, &c->d_unit_groups);
-      if (e1 == cudaSuccess)
-        e1 = cudaFuncSetAttribute(alpha_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GroupSmem));
-      if (e1 == cudaSuccess)
-        e1 = cudaFuncSetAttribute(alpha_tile_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem));
-      if (e1 == cudaSuccess)
-        e1 = cudaFuncSetAttribute(alpha_tile_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TileSmem));
-
+      if (e1 == cudaSuccess) e1 = alpha_setup_attributes();
+      if (e1 == cudaSuccess) e1 = alpha_check_setup_attributes();
       if (e1 != cudaSuccess) {
         nusi_ctx_destroy(c);
         return fail(NUSI_E_CUDA, std::string("tile setup: ") + cudaGetErrorString(e1));
@@ -357,11 +394,26 @@ int nusi_ctx_pmns2(const nusi_ctx *c, double *U2) {
   std::memcpy(U2, c->H.U2, 9 * sizeof(double));
   return NUSI_OK;
 }
-int nusi_ctx_source(const nusi_ctx *c, double *out) {
+int nusi_ctx_source(const nusi_ctx *cc, double *out) {
+  nusi_ctx *c = const_cast<nusi_ctx *>(cc);
   if (!c || !out) return NUSI_E_INVALID;
+  std::lock_guard<std::mutex> lk(c->mu);
   CU(cudaSetDevice(c->opt.device));
+  CU(cudaDeviceSynchronize());
   CU(cudaMemcpy(out, c->d_source, (size_t)(c->H.Nz - 1) * c->H.N * sizeof(double), cudaMemcpyDeviceToHost));
   return NUSI_OK;
+}
+int nusi_ctx_set_powerlaw(nusi_ctx *c, double si, double norm) {
+  if (!c) return NUSI_E_INVALID;
+  if (c->opt.source_model != 1) return fail(NUSI_E_INVALID, "nusi_ctx_set_powerlaw: the context was created with source_model 0");
+  if (!(std::fabs(1 - si) > 1e-12) || !std::isfinite(si) || !std::isfinite(norm)) return fail(NUSI_E_INVALID, "si != 1 and finite; norm finite");
+  std::lock_guard<std::mutex> lk(c->mu);
+  if (c->opt.si == si && c->opt.norm == norm) return NUSI_OK;
+  CU(cudaSetDevice(c->opt.device));
+  CU(cudaDeviceSynchronize());  // nothing in flight reads the old table
+  c->opt.si = si;
+  c->opt.norm = norm;
+  return upload_source(c);
 }
 
 int nusi_grid(int N_bins_E, double lEmin, double lEmax, double zmax, int *N_steps_z, double *zmax_eff, double *Emin,
@@ -384,6 +436,16 @@ int nusi_freestream_energy(double zmax_eff, double lEmin, double lEmax, double s
   return NUSI_OK;
 }
 
+int nusi_ctx_freestream_energy(nusi_ctx *c, double *E_FS) {
+  if (!c || !E_FS) return NUSI_E_INVALID;
+  std::lock_guard<std::mutex> lk(c->mu);
+  if (c->opt.source_model == 1)
+    *E_FS = freestream_energy(c->H.zmax_eff, c->opt.lEmin, c->opt.lEmax, c->opt.si, c->opt.norm);
+  else
+    *E_FS = freestream_energy_dsnb(c->H.zmax_eff, c->opt.lEmin, c->opt.lEmax);
+  return NUSI_OK;
+}
+
 int nusi_powerlaw_source(int N_bins_E, double lEmin, double lEmax, double zmax, double si, double norm, double *out) {
   if (!out || N_bins_E < 2 || !(lEmax > lEmin) || !(zmax > 0) || !(std::fabs(1 - si) > 1e-12)) return NUSI_E_INVALID;
   HostGrid H;
@@ -393,28 +455,38 @@ int nusi_powerlaw_source(int N_bins_E, double lEmin, double lEmax, double zmax, 
   return NUSI_OK;
 }
 
-// host preparation of a batch: masses (cached per mntot), width, |U_fk|^2
+// host preparation of a batch: masses (memoised per mntot), width, |U_fk|^2
 static void prepare_points(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
                            std::vector<PointParams> &pp, std::vector<int> &st) {
   pp.resize(n);
   st.assign(n, 0);
   const bool no = c->opt.normal_ordering != 0;
+  if (c->mass_cache.size() > NUSI_MASS_CACHE_MAX) c->mass_cache.clear();  // a sampler with continuous mntot must not grow it for ever
   for (int i = 0; i < n; ++i) {
     PointParams &P = pp[i];
     std::memset(&P, 0, sizeof(P));
-    auto key = std::make_pair(mntot[i], (int)no);
+    P.majorana = c->G.majorana;
+    P.non_resonant = c->G.non_resonant;
+    P.phiphi = c->G.phiphi;
+    P.mphi = -1.0;  // kernels skip the point and write NaN
+    if (!std::isfinite(mphi[i]) || !std::isfinite(g[i]) || !(mphi[i] > 0)) {
+      st[i] = NUSI_ST_BAD_PARAM;
+      continue;
+    }
+    if (!std::isfinite(mntot[i])) {
+      st[i] = NUSI_ST_NO_MASS | NUSI_ST_BAD_PARAM;
+      continue;
+    }
+    uint64_t key;
+    std::memcpy(&key, &mntot[i], 8);
     auto it = c->mass_cache.find(key);
     if (it == c->mass_cache.end()) {
       std::array<double, 3> m = {0, 0, 0};
       const bool ok = solve_masses(mntot[i], no, m.data());
       it = c->mass_cache.emplace(key, std::make_pair(ok, m)).first;
     }
-    P.majorana = c->G.majorana;
-    P.non_resonant = c->G.non_resonant;
-    P.phiphi = c->G.phiphi;
-    if (!it->second.first || !(mphi[i] > 0)) {
+    if (!it->second.first) {
       st[i] = NUSI_ST_NO_MASS;
-      P.mphi = -1.0;  // kernels skip the point and write NaN
       continue;
     }
     P.mphi = mphi[i];
@@ -427,18 +499,28 @@ static void prepare_points(nusi_ctx *c, int n, const double *mphi, const double 
   }
 }
 
+// Grow the work space to `npts` slots.  The new buffers are allocated first and the old ones released only when
+// every allocation has succeeded, so a failure leaves the context usable at its previous capacity.
 static int ensure_workspace(nusi_ctx *c, int npts) {
   if (npts <= c->cap_points) return NUSI_OK;
-  if (c->d_rows) cudaFree(c->d_rows);
-  if (c->d_tri) cudaFree(c->d_tri);
-  if (c->d_work) cudaFree(c->d_work);
-  if (c->d_edges) cudaFree(c->d_edges);
-  c->d_rows = c->d_tri = c->d_work = c->d_edges = nullptr;
-  c->cap_points = 0;
-  CU(cudaMalloc((void **)&c->d_rows, (size_t)npts * 2 * c->H.NT * sizeof(double)));
-  CU(cudaMalloc((void **)&c->d_tri, (size_t)npts * c->tstride * sizeof(double)));
-  if (!c->G.non_resonant) CU(cudaMalloc((void **)&c->d_work, (size_t)npts * 3 * c->H.N * sizeof(double)));
-  if (c->use_tiles) CU(cudaMalloc((void **)&c->d_edges, (size_t)npts * edge_block_doubles(c->n_edges, c->H.NT) * sizeof(double)));
+  CU(cudaDeviceSynchronize());  // nothing in flight uses the old buffers
+  double *rows = nullptr, *tri = nullptr, *work = nullptr, *edges = nullptr;
+  cudaError_t e = cudaMalloc((void **)&rows, (size_t)npts * 2 * c->H.NT * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc((void **)&tri, (size_t)npts * c->tstride * sizeof(double));
+  if (e == cudaSuccess && !c->G.non_resonant) e = cudaMalloc((void **)&work, (size_t)npts * 3 * c->H.N * sizeof(double));
+  if (e == cudaSuccess && c->use_tiles)
+    e = cudaMalloc((void **)&edges, (size_t)npts * edge_block_doubles(c->n_edges, c->H.NT) * sizeof(double));
+  if (e != cudaSuccess) {
+    for (double *p : {rows, tri, work, edges})
+      if (p) cudaFree(p);
+    cudaGetLastError();
+    return fail(NUSI_E_NOMEM, std::string("work space for ") + std::to_string(npts) + " points: " + cudaGetErrorString(e));
+  }
+  free_workspace(c);
+  c->d_rows = rows;
+  c->d_tri = tri;
+  c->d_work = work;
+  c->d_edges = edges;
   c->cap_points = npts;
   return NUSI_OK;
 }
@@ -456,181 +538,130 @@ static int next_events(nusi_ctx *c, cudaEvent_t **e3) {
   return NUSI_OK;
 }
 
-// Workspace of one launch: point i of the launch uses slot wo + i of rows / tri / edges.
-struct WorkSlot {
-  double *rows, *tri, *edges;
-};
-static WorkSlot work_slot(const nusi_ctx *c, int wo) {
-  WorkSlot w;
-  w.rows = c->d_rows + (size_t)wo * 2 * c->H.NT;
-  w.tri = c->d_tri + (size_t)wo * c->tstride;
-  w.edges = c->d_edges ? c->d_edges + (size_t)wo * edge_block_doubles(c->n_edges, c->H.NT) : nullptr;
-  return w;
+// Builder arguments of one launch: point i of the launch uses slot wo + i of rows / tri / edges.
+static BuildArgs build_args(const nusi_ctx *c, int wo, const PointParams *d_params, int cnt, int *d_status, const int2 *d_groups,
+                            int ngroups) {
+  BuildArgs A;
+  A.G = c->G;
+  A.nE = c->n_edges;
+  A.params = d_params;
+  A.cnt = cnt;
+  A.status = d_status;
+  A.rows = c->d_rows + (size_t)wo * 2 * c->H.NT;
+  A.tri = c->d_tri + (size_t)wo * c->tstride;
+  A.tstride = c->tstride;
+  A.edges = c->d_edges ? c->d_edges + (size_t)wo * edge_block_doubles(c->n_edges, c->H.NT) : nullptr;
+  A.edgeE = c->d_edgeE;
+  A.tiles = c->d_tiles;
+  A.n_tiles = c->n_tiles;
+  A.ctiles = c->d_ctiles;
+  A.n_ctiles = c->n_ctiles;
+  A.groups = d_groups;
+  A.ngroups = ngroups;
+  return A;
 }
 
-// Gamma / alphaTilde rows of `cnt` points
-static int launch_rows(nusi_ctx *c, const PointParams *d_params, int cnt, int *d_status, const WorkSlot &W, cudaStream_t s,
-                       const int2 *d_groups = nullptr, int ngroups = 0) {
+// Gamma / alphaTilde rows of one launch
+static int launch_rows_stage(nusi_ctx *c, const BuildArgs &A, cudaStream_t s) {
   const DeviceGrid &G = c->G;
-  dim3 gr((G.NT + NUSI_ROWS_PER_CTA - 1) / NUSI_ROWS_PER_CTA, cnt);
-  const char *mode_env = getenv("NUSI_ALPHA_MODE");
-  const int mode = mode_env ? atoi(mode_env) : c->opt.elementary_mode;
-  if (mode >= 3 && d_groups && ngroups > 0 && G.majorana && G.non_resonant && !G.phiphi && !getenv("NUSI_ROWS_UNGROUPED")) {
-    const char *rs = getenv("NUSI_ROWS_SPLIT");
+  const bool grouped = c->opt.elementary_mode >= 3 && A.groups && A.ngroups > 0 && G.majorana && G.non_resonant && !G.phiphi &&
+                       !c->opt.rows_ungrouped;
+  int split = 1;
+  if (grouped) {
     // scan: the g-independent part of a row once per (part of a) group.  A group is shared by `split` CTAs: 4 when the
     // launch is large (the per-point part dominates, so repeating the shared part four times is cheap and the grid is
     // 4x finer), more for small launches so that the grid still fills the 148 SMs x 4 CTAs twice (each CTA keeps >= 1 point).
-    int split = 4;
-    const long long want = 1184, have = (long long)gr.x * ngroups * split;
-    if (have < want) split = (int)std::min<long long>(32, (want + (long long)gr.x * ngroups - 1) / ((long long)gr.x * ngroups));
-    if (rs && atoi(rs) > 0) split = atoi(rs);
-    dim3 gg(gr.x, ngroups, split);
-    rows_group_kernel<0><<<gg, NUSI_ROWS_PER_CTA * 3, 0, s>>>(G, d_params, d_groups, W.rows, d_status);
-    rows_group_kernel<1><<<gg, NUSI_ROWS_PER_CTA * 3, 0, s>>>(G, d_params, d_groups, W.rows, d_status);
-    c->n_launches += 2;
-    CU(cudaGetLastError());
-    return NUSI_OK;
+    split = 4;
+    const long long nblk = (G.NT + NUSI_ROWS_PER_CTA - 1) / NUSI_ROWS_PER_CTA;
+    const long long want = 1184, have = nblk * A.ngroups * split;
+    if (have < want) split = (int)std::min<long long>(32, (want + nblk * A.ngroups - 1) / (nblk * A.ngroups));
+    if (c->opt.rows_split > 0) split = c->opt.rows_split;
   }
-  rows_kernel<0><<<gr, NUSI_ROWS_PER_CTA * 3, 0, s>>>(G, d_params, W.rows, d_status);
-  rows_kernel<1><<<gr, NUSI_ROWS_PER_CTA * 3, 0, s>>>(G, d_params, W.rows, d_status);
+  CU(launch_rows(A, grouped, split, s));
   c->n_launches += 2;
-  CU(cudaGetLastError());
   return NUSI_OK;
 }
 
-// alpha table of `cnt` points
-static int launch_alpha(nusi_ctx *c, const PointParams *d_params, int cnt, int *d_status, const WorkSlot &W, cudaStream_t s,
-                        const int2 *d_groups = nullptr, int ngroups = 0) {
+// alpha table of one launch
+static int launch_alpha_stage(nusi_ctx *c, const BuildArgs &A, cudaStream_t s) {
   const DeviceGrid &G = c->G;
-  const char *mode_env = getenv("NUSI_ALPHA_MODE");
-  const int mode = mode_env ? atoi(mode_env) : c->opt.elementary_mode;
+  const int mode = c->opt.elementary_mode;
   if (c->use_tiles) {
-    const int ntask = 3 * (2 * c->n_edges + G.NT);
-    dim3 ge((ntask + 127) / 128, cnt);
-    edges_kernel<<<ge, 128, 0, s>>>(G, c->n_edges, d_params, c->d_edgeE, W.edges);
-    dim3 gt(c->n_tiles, cnt);
+    CU(launch_edges(A, s));
     // the scan builder pays off from ~1.3 points per group on (measured on B200, 8192 points: groups of 1: 45.3 ms,
     // of 2: 31.7, of 8: 18.3, of 32: 14.5; compact builder 42.0 ms)
-    if (mode >= 3 && d_groups && ngroups > 0 && !G.phiphi && (4 * (long long)ngroups <= 3 * (long long)cnt || getenv("NUSI_GROUP_ALWAYS"))) {
-      // scan builder: one CTA per (tile, group of points with the same mphi and neutrino masses)
-      dim3 gg(c->n_ctiles, ngroups);
-      alpha_group_kernel<<<gg, 256, sizeof(GroupSmem), s>>>(G, c->n_edges, d_params, W.edges, c->d_ctiles, d_groups, W.tri, c->tstride, d_status);
-    } else if (mode >= 2) {
-      dim3 gc(c->n_ctiles, cnt);
-      alpha_compact_kernel<<<gc, 256, 0, s>>>(G, c->n_edges, d_params, W.edges, c->d_ctiles, W.tri, c->tstride, d_status);
-    } else if (mode == 0)
-      alpha_tile_kernel<0><<<gt, 256, sizeof(TileSmem), s>>>(G, c->n_edges, d_params, c->d_edgeE, W.edges, c->d_tiles, W.tri,
-                                                            c->tstride, d_status);
+    if (mode >= 3 && A.groups && A.ngroups > 0 && !G.phiphi && (4 * (long long)A.ngroups <= 3 * (long long)A.cnt || c->opt.group_always))
+      CU(launch_alpha_group(A, s));  // one CTA per (tile, group of points with the same mphi and neutrino masses)
+    else if (mode >= 2)
+      CU(launch_alpha_compact(A, s));
     else
-      alpha_tile_kernel<1><<<gt, 256, sizeof(TileSmem), s>>>(G, c->n_edges, d_params, c->d_edgeE, W.edges, c->d_tiles, W.tri,
-                                                            c->tstride, d_status);
+      CU(launch_alpha_tile(A, mode, s));
     c->n_launches += 2;
   } else {
-    const long long nent = G.non_resonant ? (long long)G.NT * (G.NT - 1) / 2 : (long long)(G.NT - 1);
-    dim3 ga((unsigned)((nent + 127) / 128), cnt);
-    alpha_kernel<<<ga, 128, 0, s>>>(G, d_params, W.tri, c->tstride, d_status, mode >= 2 ? 1 : 0);
+    CU(launch_alpha_entry(A, mode >= 2 ? 1 : 0, s));
     c->n_launches += 1;
   }
-  CU(cudaGetLastError());
   return NUSI_OK;
 }
 
-static int launch_integrate(nusi_ctx *c, const PointParams *d_params, int cnt, double *d_fm, double *d_ff,
-                            const WorkSlot &W, int wo, cudaStream_t s) {
-  const DeviceGrid &G = c->G;
-  double *const d_work = c->d_work ? c->d_work + (size_t)wo * 3 * c->H.N : nullptr;
-  if (G.non_resonant) {
-    const int N = G.N, NT = G.NT, S = G.Nz - 1;
-    if (getenv("NUSI_SERIAL_INTEGRATOR")) {  // reference-shaped bin-by-bin kernel, kept for cross-checks
-      if (N > 256) return fail(NUSI_E_INVALID, "serial integrator supports N_bins_E <= 256");
-      integrate_kernel<1><<<cnt, ((N + 31) / 32) * 32, 0, s>>>(G, d_params, W.rows, W.tri, c->tstride, d_fm, d_ff);
-    } else if (getenv("NUSI_WAVE_INTEGRATOR")) {  // bin-owned accumulators, kept for cross-checks
-#define NUSI_WAVE(BPT, SB, NST)                                                                             \
-  do {                                                                                                      \
-    const size_t sh = (size_t)((NST + 2) * NT + 2 * 32 + 2 * S) * sizeof(double);                           \
-    CU(cudaFuncSetAttribute(integrate_wave_kernel<BPT, SB, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
-    integrate_wave_kernel<BPT, SB, NST><<<cnt, 256, sh, s>>>(G, d_params, W.rows, W.tri, c->tstride, d_fm, d_ff); \
-  } while (0)
-      if (N <= 256 && NT <= 256 * 3)
-        NUSI_WAVE(1, 32, 8);
-      else if (N <= 512 && NT <= 256 * 4)
-        NUSI_WAVE(2, 16, 8);
-      else if (N <= 1024 && NT <= 256 * 6)
-        NUSI_WAVE(4, 8, 8);
-      else if (N <= 2048 && NT <= 256 * 10)
-        NUSI_WAVE(8, 4, 6);
-      else
-        return fail(NUSI_E_INVALID, "N_bins_E > 2048 is not supported by the integrator");
-#undef NUSI_WAVE
-    } else {
-      // diagonal-owned accumulators: N <= 256 BPT bins, N + SB - 1 <= 256 DPT diagonals, NT <= 256 (BPT + 2) table rows
-#define NUSI_DIAG(BPT, SB, DPT, NST)                                                                        \
-  do {                                                                                                      \
-    const size_t sh = (size_t)((NST + 2) * NT + 2 * SB + 2 * SB * NUSI_PRE_DOUBLES + 2 * S + 2 * N + 2) * sizeof(double); \
-    CU(cudaFuncSetAttribute(integrate_diag_kernel<BPT, SB, DPT, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
-    integrate_diag_kernel<BPT, SB, DPT, NST><<<cnt, 256, sh, s>>>(G, d_params, W.rows, W.tri, c->tstride, d_fm, d_ff); \
-  } while (0)
-      // More threads per point for finer binning = fewer bins and diagonals per thread, so wide bands still fit the
-      // registers and the table is streamed fewer times (bands x waves is what a latency-bound point pays for).
-      // NUSI_FINE_VARIANT=0 selects the 256-thread configurations throughout (kept for comparison).
-#define NUSI_DIAG_T(BPT, SB, DPT, NST, NTHR)                                                                \
-  do {                                                                                                      \
-    const size_t sh = (size_t)((NST + 2) * NT + 2 * SB + 2 * SB * NUSI_PRE_DOUBLES + 2 * S + 2 * N + 2) * sizeof(double); \
-    CU(cudaFuncSetAttribute(integrate_diag_kernel<BPT, SB, DPT, NST, NTHR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh)); \
-    integrate_diag_kernel<BPT, SB, DPT, NST, NTHR><<<cnt, NTHR, sh, s>>>(G, d_params, W.rows, W.tri, c->tstride, d_fm, d_ff); \
-  } while (0)
-      const char *fv = getenv("NUSI_FINE_VARIANT");
-      const bool wide = !(fv && atoi(fv) == 0);
-      if (N <= 225 && NT <= 256 && !getenv("NUSI_DIAG_PRE3")) {  // a table column fits one row per thread (N_E = 200: NT = 231)
-        const size_t sh = (size_t)((8 + 2) * NT + 2 * NUSI_DIAG_SB_SMALL + 2 * NUSI_DIAG_SB_SMALL * NUSI_PRE_DOUBLES + 2 * S + 2 * N + 2) * sizeof(double);
-        CU(cudaFuncSetAttribute(integrate_diag_kernel<1, NUSI_DIAG_SB_SMALL, 1, 8, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
-        integrate_diag_kernel<1, NUSI_DIAG_SB_SMALL, 1, 8, 256, 1><<<cnt, 256, sh, s>>>(G, d_params, W.rows, W.tri, c->tstride, d_fm, d_ff);
-      } else if (N <= 225 && NT <= 256 * 3)
-        NUSI_DIAG(1, NUSI_DIAG_SB_SMALL, 1, 8);
-      else if (N <= 256 && NT <= 256 * 3)
-        NUSI_DIAG(1, 32, 2, 8);
-      else if (wide && N + 32 - 1 <= 512 && NT <= 512 * 3)
-        NUSI_DIAG_T(1, 32, 1, 8, 512);
-      else if (N <= 512 && NT <= 256 * 4)
-        NUSI_DIAG(2, 16, 3, 8);
-      else if (wide && N <= 1024 && NT <= 512 * 4)
-        NUSI_DIAG_T(2, 16, 3, 8, 512);
-      else if (N <= 1024 && NT <= 256 * 6)
-        NUSI_DIAG(4, 8, 5, 8);
-      else if (wide && N + 8 - 1 <= 512 * 4 && NT <= 512 * 6)
-        NUSI_DIAG_T(4, 8, 4, 6, 512);
-      else if (N <= 2048 && NT <= 256 * 10)
-        NUSI_DIAG(8, 4, 9, 6);
-      else
-        return fail(NUSI_E_INVALID, "N_bins_E > 2048 is not supported by the integrator");
-#undef NUSI_DIAG_T
-#undef NUSI_DIAG
-    }
-  } else {
-    integrate_resonant_kernel<<<(cnt + 63) / 64, 64, 0, s>>>(G, cnt, d_params, W.rows, W.tri, c->tstride,
-                                                             d_work, d_fm, d_ff);
-  }
+static int launch_integrate_stage(nusi_ctx *c, const IntegArgs &A, cudaStream_t s) {
+  cudaError_t e;
+  if (!c->G.non_resonant)
+    e = launch_integrate_resonant(A, s);
+  else if (c->opt.integrator == 2)
+    e = launch_integrate_serial(A, s);
+  else if (c->opt.integrator == 1)
+    e = launch_integrate_wave(A, s);
+  else
+    e = launch_integrate_diag(A, c->opt.fine_variant, s);
+  if (e == cudaErrorInvalidValue) return fail(NUSI_E_INVALID, "binning not supported by the selected integrator");
+  CU(e);
   c->n_launches += 1;
-  CU(cudaGetLastError());
   return NUSI_OK;
 }
 
-// One device block per points object: [params | groups | status0], filled by ONE host->device copy.  pooled: the block
-// is the context's own (grown on demand, kept across calls) -- nusi_evolve_batch, which would otherwise pay three
-// cudaMalloc + three cudaFree (each a device synchronisation) per call.
+// One device block per points object: [params | groups | status0 | statw | out_index], filled by ONE host->device
+// copy.  pooled: the block is the context's own (grown on demand, kept across calls) -- nusi_evolve_batch, which would
+// otherwise pay a cudaMalloc + cudaFree (each a device synchronisation) per call.
 static int points_create_impl(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
                               nusi_points **out, bool pooled) {
   if (!c || !out || n <= 0 || !mphi || !g || !mntot) return NUSI_E_INVALID;
   CU(cudaSetDevice(c->opt.device));
-  std::vector<PointParams> pp;
+  std::vector<PointParams> pp0, pp;
+  std::vector<int> st0;
   nusi_points *p = new nusi_points;
   p->n = n;
   p->device = c->opt.device;
-  prepare_points(c, n, mphi, g, mntot, pp, p->h_status0);
+  prepare_points(c, n, mphi, g, mntot, pp0, st0);
+  // evolve order: stable sort by (mphi, m_nu) -- the points of a scan row become neighbours whatever order the caller
+  // used (g-major grids, shuffled samples); rejected points (mphi = -1) go first
+  std::vector<int> order(n);
+  std::iota(order.begin(), order.end(), 0);
+  auto key_less = [&](int a, int b) {
+    const PointParams &A = pp0[a], &B = pp0[b];
+    if (A.mphi != B.mphi) return A.mphi < B.mphi;
+    if (A.mn[0] != B.mn[0]) return A.mn[0] < B.mn[0];
+    return A.mn[2] < B.mn[2];
+  };
+  if (!c->opt.keep_order && c->opt.elementary_mode >= 3 && !std::is_sorted(order.begin(), order.end(), key_less))
+    std::stable_sort(order.begin(), order.end(), key_less);
+  p->reordered = false;
+  for (int i = 0; i < n; ++i) p->reordered = p->reordered || order[i] != i;
+  if (p->reordered) {
+    pp.resize(n);
+    std::vector<int> st(n);
+    for (int i = 0; i < n; ++i) {
+      pp[i] = pp0[order[i]];
+      st[i] = st0[order[i]];
+    }
+    st0.swap(st);
+    p->h_out_index = order;
+  } else {
+    pp.swap(pp0);
+  }
   std::vector<int2> groups;
   {
-    const char *gm = getenv("NUSI_GROUP_MAX");
-    const int gmax = gm ? (atoi(gm) > 0 ? (atoi(gm) < NUSI_GROUP_CAP ? atoi(gm) : NUSI_GROUP_CAP) : 1) : 32;
+    const int gmax = c->opt.group_max > 0 ? std::min(c->opt.group_max, NUSI_GROUP_CAP) : 32;
     p->SL = c->max_chunk < NUSI_SLICE ? c->max_chunk : NUSI_SLICE;
     for (int off = 0; off < n; off += p->SL) {
       p->slice_g0.push_back((int)groups.size());
@@ -647,17 +678,29 @@ static int points_create_impl(nusi_ctx *c, int n, const double *mphi, const doub
     }
     p->slice_g0.push_back((int)groups.size());
   }
-  const size_t o_groups = ((size_t)n * sizeof(PointParams) + 15) & ~(size_t)15;
-  const size_t o_status = o_groups + ((groups.size() * sizeof(int2) + 15) & ~(size_t)15);
-  const size_t bytes = o_status + (size_t)n * sizeof(int);
+  c->last_groups = (int)groups.size();
+  c->last_grouped_points = 0;
+  for (const int2 &gp : groups)
+    if (gp.y > 1) c->last_grouped_points += gp.y;
+  c->last_reordered = p->reordered ? 1 : 0;
+
+  auto al16 = [](size_t b) { return (b + 15) & ~(size_t)15; };
+  const size_t o_groups = al16((size_t)n * sizeof(PointParams));
+  const size_t o_status = o_groups + al16(groups.size() * sizeof(int2));
+  const size_t o_statw = o_status + al16((size_t)n * sizeof(int));
+  const size_t o_index = o_statw + al16((size_t)n * sizeof(int));
+  const size_t bytes = o_index + (p->reordered ? al16((size_t)n * sizeof(int)) : 0);
   std::vector<unsigned char> stage(bytes);
   std::memcpy(stage.data(), pp.data(), (size_t)n * sizeof(PointParams));
   std::memcpy(stage.data() + o_groups, groups.data(), groups.size() * sizeof(int2));
-  std::memcpy(stage.data() + o_status, p->h_status0.data(), (size_t)n * sizeof(int));
+  std::memcpy(stage.data() + o_status, st0.data(), (size_t)n * sizeof(int));
+  std::memcpy(stage.data() + o_statw, st0.data(), (size_t)n * sizeof(int));
+  if (p->reordered) std::memcpy(stage.data() + o_index, order.data(), (size_t)n * sizeof(int));
   cudaError_t e = cudaSuccess;
   unsigned char *base = nullptr;
   if (pooled) {
     if (bytes > c->pool_cap) {
+      cudaDeviceSynchronize();
       if (c->d_pool) cudaFree(c->d_pool);
       c->d_pool = nullptr;
       c->pool_cap = 0;
@@ -674,6 +717,8 @@ static int points_create_impl(nusi_ctx *c, int n, const double *mphi, const doub
     p->d_params = reinterpret_cast<PointParams *>(base);
     p->d_groups = reinterpret_cast<int2 *>(base + o_groups);
     p->d_status0 = reinterpret_cast<int *>(base + o_status);
+    p->d_statw = reinterpret_cast<int *>(base + o_statw);
+    p->d_out_index = p->reordered ? reinterpret_cast<int *>(base + o_index) : nullptr;
     e = cudaMemcpy(base, stage.data(), bytes, cudaMemcpyHostToDevice);
   }
   if (e != cudaSuccess) {
@@ -685,6 +730,8 @@ static int points_create_impl(nusi_ctx *c, int n, const double *mphi, const doub
 }
 int nusi_points_create(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
                        nusi_points **out) {
+  if (!c) return NUSI_E_INVALID;
+  std::lock_guard<std::mutex> lk(c->mu);
   return points_create_impl(c, n, mphi, g, mntot, out, false);
 }
 void nusi_points_destroy(nusi_points *p) {
@@ -696,21 +743,28 @@ void nusi_points_destroy(nusi_points *p) {
   delete p;
 }
 int nusi_points_count(const nusi_points *p) { return p ? p->n : 0; }
+int nusi_last_grouping(const nusi_ctx *c, int *n_groups, int *n_grouped_points, int *reordered) {
+  if (!c) return NUSI_E_INVALID;
+  if (n_groups) *n_groups = c->last_groups;
+  if (n_grouped_points) *n_grouped_points = c->last_grouped_points;
+  if (reordered) *reordered = c->last_reordered;
+  return NUSI_OK;
+}
 
 // ------------------------------------------------------------------------------------------------------
-// The evolve pipeline.  A batch is cut into slices of NUSI_SLICE points.  Per slice k:
-//     stream s_i (high priority):  rows(k)                      wait table(k)   integrate(k)
-//     stream s_x                :  edges(k) + alpha table(k) ------^       edges(k+1) + alpha table(k+1) ...
-// With host buffers each slice's fluxes go home on a copy stream under the next slice's kernels (always on).
-// The two-stream compute overlap drawn above is OPT-IN (NUSI_OVERLAP=1): measured on B200 it is neutral
-// (29.8 vs 29.9 ms per 4096 points) -- the builder already owns every register of an SM at 4 CTAs/SM, so the
-// integrator's CTAs displace builder CTAs one for one -- and it blurs the per-kernel event times.  By default
-// all kernels run on the caller's stream in order.
+// The evolve pipeline.  A batch is cut into slices of NUSI_SLICE points (evolve order).  Per slice k, in stream order:
+//     rows(k)   edges(k) + alpha table(k)   integrate(k)  [-> D2H(k) on the copy stream, under slice k+1's kernels]
+// Outputs land in slot out_index[i] of the output arrays (the caller's order).  With host buffers and an unchanged
+// order, each slice's fluxes go home on the copy stream as soon as its integrator has finished; with a reordered
+// batch a slice's outputs are scattered over the arrays, so they go home in caller-order pieces after the last slice.
+// opts.two_stream puts the builder and rows + integrator on two streams (measured neutral on B200: the builder
+// already owns every register of an SM, so the integrator's CTAs displace builder CTAs one for one).
 // ------------------------------------------------------------------------------------------------------
 static int ensure_streams(nusi_ctx *c) {
-  if (c->s_x) return NUSI_OK;
+  if (c->s_main) return NUSI_OK;
   int lo = 0, hi = 0;
   CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+  CU(cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, lo));
   CU(cudaStreamCreateWithPriority(&c->s_x, cudaStreamNonBlocking, lo));
   CU(cudaStreamCreateWithPriority(&c->s_i, cudaStreamNonBlocking, hi));
   CU(cudaStreamCreateWithPriority(&c->s_copy, cudaStreamNonBlocking, hi));
@@ -727,21 +781,33 @@ static int slice_event(std::vector<cudaEvent_t> &v, size_t k, cudaEvent_t *out) 
   return NUSI_OK;
 }
 
-// d_fm / d_ff / d_st: device outputs indexed from the batch start.  h_*: optional host destinations (same shapes).
+// Host destinations of nusi_evolve_batch.  direct: the caller's buffers are page-locked, copies go straight there;
+// otherwise through the context's page-locked staging area and a host memcpy per piece (a cudaMemcpyAsync into
+// pageable memory would block the host until the slice has finished and serialise the whole pipeline).
+struct HostOut {
+  double *fm = nullptr, *ff = nullptr;
+  int *st = nullptr;
+  bool direct = false;
+  double *s_fm = nullptr, *s_ff = nullptr;  // staging (whole batch, same indexing as the destinations)
+  int *s_st = nullptr;
+  bool any() const { return fm || ff || st; }
+};
+
+// d_fm / d_ff / d_st: device outputs indexed by the caller's point index.
 static int run_pipeline(nusi_ctx *c, const nusi_points *p, double *d_fm, double *d_ff, int *d_st, cudaStream_t caller,
-                        double *h_fm, double *h_ff, int *h_st) {
+                        const HostOut *ho) {
   const int N = c->H.N;
-  const bool to_host = h_fm || h_ff || h_st;
-  const bool overlap = getenv("NUSI_OVERLAP") != nullptr;
+  const bool to_host = ho && ho->any();
+  const bool overlap = c->opt.two_stream != 0;
   int rc = ensure_streams(c);
   if (rc) return rc;
-  // slice size SL; the workspace holds a whole number of slices (all of them when the batch fits)
+  // slice size SL; the workspace holds a whole number of slices (all of them when the batch fits), or just the batch
   const int SL = c->max_chunk < NUSI_SLICE ? c->max_chunk : NUSI_SLICE;
-  const int chunk = p->n <= c->max_chunk ? ((p->n + SL - 1) / SL) * SL : (c->max_chunk / SL) * SL;
+  const int chunk = p->n <= SL ? p->n : (p->n <= c->max_chunk ? ((p->n + SL - 1) / SL) * SL : std::max(1, c->max_chunk / SL) * SL);
   if ((rc = ensure_workspace(c, chunk))) return rc;
   c->ev_used = 0;
   c->n_launches = 0;
-  cudaStream_t sx = overlap ? c->s_x : caller, si = overlap ? c->s_i : caller, sc = (overlap || to_host) ? c->s_copy : caller;
+  cudaStream_t sx = overlap ? c->s_x : caller, si = overlap ? c->s_i : caller, sc = to_host ? c->s_copy : caller;
   if (overlap || to_host) {
     CU(cudaEventRecord(c->ev_fork, caller));
     if (overlap) {
@@ -749,11 +815,28 @@ static int run_pipeline(nusi_ctx *c, const nusi_points *p, double *d_fm, double 
       CU(cudaStreamWaitEvent(si, c->ev_fork, 0));
     }
   }
+  // the builder kernels OR their warning bits into the working copy of the host-side status
+  CU(cudaMemcpyAsync(p->d_statw, p->d_status0, (size_t)p->n * sizeof(int), cudaMemcpyDeviceToDevice, si));
+  if (overlap) {
+    CU(cudaEventRecord(c->ev_ji, si));
+    CU(cudaStreamWaitEvent(sx, c->ev_ji, 0));
+  }
+  const bool per_slice_copy = to_host && !p->reordered;
+  auto copy_piece = [&](int off, int cnt, size_t k) -> int {  // outputs [off, off + cnt) (caller order) -> host
+    const size_t o = (size_t)off * 3 * N, b = (size_t)cnt * 3 * N * sizeof(double);
+    if (ho->fm) CU(cudaMemcpyAsync((ho->direct ? ho->fm : ho->s_fm) + o, d_fm + o, b, cudaMemcpyDeviceToHost, sc));
+    if (ho->ff) CU(cudaMemcpyAsync((ho->direct ? ho->ff : ho->s_ff) + o, d_ff + o, b, cudaMemcpyDeviceToHost, sc));
+    if (ho->st) CU(cudaMemcpyAsync((ho->direct ? ho->st : ho->s_st) + off, d_st + off, (size_t)cnt * sizeof(int), cudaMemcpyDeviceToHost, sc));
+    cudaEvent_t evc;
+    int r = slice_event(c->ev_copied, k, &evc);
+    if (r) return r;
+    CU(cudaEventRecord(evc, sc));
+    return NUSI_OK;
+  };
   size_t k = 0;
   for (int off = 0; off < p->n; off += SL, ++k) {
     const int cnt = (p->n - off < SL) ? p->n - off : SL;
     const int wo = off % chunk;  // the slices of one chunk use distinct workspace slots
-    const WorkSlot W = work_slot(c, wo);
     cudaEvent_t *t6, ev_tab, ev_out;
     if ((rc = next_events(c, &t6))) return rc;
     if ((rc = slice_event(c->ev_alpha, k, &ev_tab))) return rc;
@@ -761,39 +844,41 @@ static int run_pipeline(nusi_ctx *c, const nusi_points *p, double *d_fm, double 
       CU(cudaEventRecord(c->ev_ji, si));
       CU(cudaStreamWaitEvent(sx, c->ev_ji, 0));
     }
-    CU(cudaEventRecord(t6[0], si));
     const bool grouped = (p->SL == SL) && p->d_groups && k + 1 < p->slice_g0.size();
-    if ((rc = launch_rows(c, p->d_params + off, cnt, d_st + off, W, si, grouped ? p->d_groups + p->slice_g0[k] : nullptr,
-                          grouped ? p->slice_g0[k + 1] - p->slice_g0[k] : 0)))
-      return rc;
+    const BuildArgs B = build_args(c, wo, p->d_params + off, cnt, p->d_statw + off, grouped ? p->d_groups + p->slice_g0[k] : nullptr,
+                                   grouped ? p->slice_g0[k + 1] - p->slice_g0[k] : 0);
+    CU(cudaEventRecord(t6[0], si));
+    if ((rc = launch_rows_stage(c, B, si))) return rc;
     CU(cudaEventRecord(t6[1], si));
     CU(cudaEventRecord(t6[2], sx));
-    if ((rc = launch_alpha(c, p->d_params + off, cnt, d_st + off, W, sx, grouped ? p->d_groups + p->slice_g0[k] : nullptr,
-                           grouped ? p->slice_g0[k + 1] - p->slice_g0[k] : 0)))
-      return rc;
+    if ((rc = launch_alpha_stage(c, B, sx))) return rc;
     CU(cudaEventRecord(t6[3], sx));
     if (overlap) {
       CU(cudaEventRecord(ev_tab, sx));
       CU(cudaStreamWaitEvent(si, ev_tab, 0));
     }
     CU(cudaEventRecord(t6[4], si));
-    double *fm = d_fm ? d_fm + (size_t)off * 3 * N : nullptr;
-    double *ff = d_ff ? d_ff + (size_t)off * 3 * N : nullptr;
-    if ((rc = launch_integrate(c, p->d_params + off, cnt, fm, ff, W, wo, si))) return rc;
+    IntegArgs I;
+    I.G = c->G;
+    I.params = p->d_params + off;
+    I.cnt = cnt;
+    I.rows = B.rows;
+    I.tri = B.tri;
+    I.tstride = c->tstride;
+    I.work = c->d_work ? c->d_work + (size_t)wo * 3 * N : nullptr;
+    // identity order: offset the output arrays instead of indexing them
+    I.flux_mass = d_fm ? (p->reordered ? d_fm : d_fm + (size_t)off * 3 * N) : nullptr;
+    I.flux_fla = d_ff ? (p->reordered ? d_ff : d_ff + (size_t)off * 3 * N) : nullptr;
+    I.out_index = p->reordered ? p->d_out_index + off : nullptr;
+    I.status_in = p->d_statw + off;
+    I.status_out = d_st ? (p->reordered ? d_st : d_st + off) : nullptr;
+    if ((rc = launch_integrate_stage(c, I, si))) return rc;
     CU(cudaEventRecord(t6[5], si));
-    if (to_host) {
+    if (per_slice_copy) {
       if ((rc = slice_event(c->ev_done, k, &ev_out))) return rc;
-      if (overlap) {  // the status words are complete when rows, builder and integrator of the slice are
-        CU(cudaEventRecord(ev_out, si));
-        CU(cudaStreamWaitEvent(sc, ev_out, 0));
-      } else {
-        CU(cudaEventRecord(ev_out, caller));
-        CU(cudaStreamWaitEvent(sc, ev_out, 0));
-      }
-      const size_t o = (size_t)off * 3 * N, b = (size_t)cnt * 3 * N * sizeof(double);
-      if (h_fm) CU(cudaMemcpyAsync(h_fm + o, d_fm + o, b, cudaMemcpyDeviceToHost, sc));
-      if (h_ff) CU(cudaMemcpyAsync(h_ff + o, d_ff + o, b, cudaMemcpyDeviceToHost, sc));
-      if (h_st) CU(cudaMemcpyAsync(h_st + off, d_st + off, (size_t)cnt * sizeof(int), cudaMemcpyDeviceToHost, sc));
+      CU(cudaEventRecord(ev_out, si));
+      CU(cudaStreamWaitEvent(sc, ev_out, 0));
+      if ((rc = copy_piece(off, cnt, k))) return rc;
     }
   }
   // join
@@ -802,6 +887,24 @@ static int run_pipeline(nusi_ctx *c, const nusi_points *p, double *d_fm, double 
     CU(cudaEventRecord(c->ev_ji, si));
     CU(cudaStreamWaitEvent(caller, c->ev_jx, 0));
     CU(cudaStreamWaitEvent(caller, c->ev_ji, 0));
+  }
+  size_t npieces = per_slice_copy ? k : 0;
+  if (to_host && !per_slice_copy) {  // reordered batch: everything is computed; home in caller-order pieces
+    CU(cudaEventRecord(c->ev_jx, caller));
+    CU(cudaStreamWaitEvent(sc, c->ev_jx, 0));
+    for (int off = 0; off < p->n; off += SL, ++npieces)
+      if ((rc = copy_piece(off, std::min(SL, p->n - off), npieces))) return rc;
+  }
+  if (to_host && !ho->direct) {  // staging -> the caller's pageable buffers, piece by piece as the copies complete
+    size_t q = 0;
+    for (int off = 0; off < p->n; off += SL, ++q) {
+      const int cnt = std::min(SL, p->n - off);
+      CU(cudaEventSynchronize(c->ev_copied[q]));
+      const size_t o = (size_t)off * 3 * N, b = (size_t)cnt * 3 * N * sizeof(double);
+      if (ho->fm) std::memcpy(ho->fm + o, ho->s_fm + o, b);
+      if (ho->ff) std::memcpy(ho->ff + o, ho->s_ff + o, b);
+      if (ho->st) std::memcpy(ho->st + off, ho->s_st + off, (size_t)cnt * sizeof(int));
+    }
   }
   if (to_host) {
     CU(cudaEventRecord(c->ev_jc, sc));
@@ -812,26 +915,35 @@ static int run_pipeline(nusi_ctx *c, const nusi_points *p, double *d_fm, double 
 
 int nusi_evolve_points(nusi_ctx *c, const nusi_points *p, double *d_fm, double *d_ff, int *d_status, void *stream) {
   if (!c || !p) return NUSI_E_INVALID;
+  std::lock_guard<std::mutex> lk(c->mu);
   CU(cudaSetDevice(c->opt.device));
-  cudaStream_t s = (cudaStream_t)stream;
-  int *d_st = d_status ? d_status : p->d_status0;
-  if (d_status) CU(cudaMemcpyAsync(d_status, p->d_status0, (size_t)p->n * sizeof(int), cudaMemcpyDeviceToDevice, s));
-  return run_pipeline(c, p, d_fm, d_ff, d_st, s, nullptr, nullptr, nullptr);
+  return run_pipeline(c, p, d_fm, d_ff, d_status, (cudaStream_t)stream, nullptr);
 }
 
-// Host buffers in, host buffers out: the pipeline above with the device->host copy of every finished slice on
-// a copy stream (effective when the caller's buffers are page-locked; with pageable memory the driver stages
-// the copies, still correct).
+static bool is_pinned(const void *ptr) {
+  if (!ptr) return true;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, ptr) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost;
+}
+
+// Host buffers in, host buffers out.
 int nusi_evolve_batch(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot,
                       double *flux_mass, double *flux_fla, int *status) {
   if (!c || n <= 0 || !mphi || !g || !mntot) return NUSI_E_INVALID;
+  std::lock_guard<std::mutex> lk(c->mu);
   CU(cudaSetDevice(c->opt.device));
   const int N = c->H.N;
   if (n > c->out_cap) {
-    if (c->d_out_fm) cudaFree(c->d_out_fm);
-    if (c->d_out_ff) cudaFree(c->d_out_ff);
+    CU(cudaDeviceSynchronize());
+    for (double **q : {&c->d_out_fm, &c->d_out_ff}) {
+      if (*q) cudaFree(*q);
+      *q = nullptr;
+    }
     if (c->d_out_st) cudaFree(c->d_out_st);
-    c->d_out_fm = c->d_out_ff = nullptr;
     c->d_out_st = nullptr;
     c->out_cap = 0;
     CU(cudaMalloc((void **)&c->d_out_fm, (size_t)n * 3 * N * sizeof(double)));
@@ -841,43 +953,76 @@ int nusi_evolve_batch(nusi_ctx *c, int n, const double *mphi, const double *g, c
   }
   int rc = ensure_streams(c);
   if (rc) return rc;
+  HostOut ho;
+  ho.fm = flux_mass;
+  ho.ff = flux_fla;
+  ho.st = status;
+  ho.direct = is_pinned(flux_mass) && is_pinned(flux_fla) && is_pinned(status);
+  if (ho.any() && !ho.direct) {
+    const size_t bf = (size_t)n * 3 * N * sizeof(double), need = 2 * bf + (size_t)n * sizeof(int);
+    if (need > c->h_stage_cap) {
+      if (c->h_stage) cudaFreeHost(c->h_stage);
+      c->h_stage = nullptr;
+      c->h_stage_cap = 0;
+      CU(cudaMallocHost((void **)&c->h_stage, need));
+      c->h_stage_cap = need;
+    }
+    ho.s_fm = reinterpret_cast<double *>(c->h_stage);
+    ho.s_ff = reinterpret_cast<double *>(c->h_stage + bf);
+    ho.s_st = reinterpret_cast<int *>(c->h_stage + 2 * bf);
+  }
   nusi_points *p = nullptr;
   if ((rc = points_create_impl(c, n, mphi, g, mntot, &p, true))) return rc;
-  cudaStream_t s = c->s_copy;  // any stream of ours serves as the "caller" of the pipeline
-  cudaError_t e = cudaMemcpyAsync(c->d_out_st, p->d_status0, (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, s);
-  if (e == cudaSuccess)
-    rc = run_pipeline(c, p, flux_mass ? c->d_out_fm : nullptr, flux_fla ? c->d_out_ff : nullptr, c->d_out_st, s, flux_mass,
-                      flux_fla, status);
+  rc = run_pipeline(c, p, flux_mass ? c->d_out_fm : nullptr, flux_fla ? c->d_out_ff : nullptr, c->d_out_st, c->s_main, &ho);
   cudaError_t e2 = cudaDeviceSynchronize();
   nusi_points_destroy(p);
   if (rc) return rc;
-  if (e == cudaSuccess) e = e2;
-  if (e != cudaSuccess) return fail(NUSI_E_CUDA, std::string("evolve_batch: ") + cudaGetErrorString(e));
+  if (e2 != cudaSuccess) return fail(NUSI_E_CUDA, std::string("evolve_batch: ") + cudaGetErrorString(e2));
+  return NUSI_OK;
+}
+
+int nusi_energy_integral(nusi_ctx *c, int n, const double *d_flux_mass, double *E_int, void *stream) {
+  if (!c || n <= 0 || !d_flux_mass || !E_int) return NUSI_E_INVALID;
+  std::lock_guard<std::mutex> lk(c->mu);
+  CU(cudaSetDevice(c->opt.device));
+  if (n > c->eint_cap) {
+    if (c->d_eint) cudaFree(c->d_eint);
+    c->d_eint = nullptr;
+    c->eint_cap = 0;
+    CU(cudaMalloc((void **)&c->d_eint, (size_t)n * sizeof(double)));
+    c->eint_cap = n;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  CU(launch_energy_integral(n, c->H.N, d_flux_mass, c->d_wE2, c->d_eint, s));
+  CU(cudaMemcpyAsync(E_int, c->d_eint, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
   return NUSI_OK;
 }
 
 int nusi_tables_batch(nusi_ctx *c, int n, const double *mphi, const double *g, const double *mntot, double *Gamma,
                       double *alphaTilde, double *alpha, int *status) {
   if (!c || n <= 0 || !mphi || !g || !mntot) return NUSI_E_INVALID;
+  std::lock_guard<std::mutex> lk(c->mu);
   CU(cudaSetDevice(c->opt.device));
   const int NT = c->H.NT;
   nusi_points *p = nullptr;
-  int rc = nusi_points_create(c, n, mphi, g, mntot, &p);
+  int rc = points_create_impl(c, n, mphi, g, mntot, &p, false);
   if (rc) return rc;
   c->ev_used = 0;
   c->n_launches = 0;
   std::vector<double> hrows((size_t)2 * NT), htri(c->tstride);
+  std::vector<int> hst(n);
   // group by group, through the same builder a batch of these points gets in nusi_evolve_batch
   for (size_t gi = 0; gi < p->h_groups.size() && rc == NUSI_OK; ++gi) {
     const int i0 = p->h_groups[gi].x, len = p->h_groups[gi].y;
     rc = ensure_workspace(c, len);
     if (rc) break;
-    const WorkSlot W = work_slot(c, 0);
-    rc = launch_rows(c, p->d_params + i0, len, p->d_status0 + i0, W, nullptr, c->d_unit_groups ? c->d_unit_groups + len : nullptr, 1);
-    if (rc == NUSI_OK)
-      rc = launch_alpha(c, p->d_params + i0, len, p->d_status0 + i0, W, nullptr, c->d_unit_groups ? c->d_unit_groups + len : nullptr, 1);
+    const BuildArgs B = build_args(c, 0, p->d_params + i0, len, p->d_statw + i0, c->d_unit_groups ? c->d_unit_groups + len : nullptr, 1);
+    rc = launch_rows_stage(c, B, nullptr);
+    if (rc == NUSI_OK) rc = launch_alpha_stage(c, B, nullptr);
     if (rc) break;
     for (int i = i0; i < i0 + len; ++i) {
+      const int dst = p->reordered ? p->h_out_index[i] : i;  // the caller's index of this point
       cudaError_t e = cudaMemcpy(hrows.data(), c->d_rows + (size_t)(i - i0) * 2 * NT, hrows.size() * sizeof(double), cudaMemcpyDeviceToHost);
       if (e == cudaSuccess)
         e = cudaMemcpy(htri.data(), c->d_tri + (size_t)(i - i0) * c->tstride, htri.size() * sizeof(double), cudaMemcpyDeviceToHost);
@@ -885,10 +1030,10 @@ int nusi_tables_batch(nusi_ctx *c, int n, const double *mphi, const double *g, c
         rc = fail(NUSI_E_CUDA, std::string("tables_batch: ") + cudaGetErrorString(e));
         break;
       }
-      if (Gamma) std::memcpy(Gamma + (size_t)i * NT, hrows.data(), NT * sizeof(double));
-      if (alphaTilde) std::memcpy(alphaTilde + (size_t)i * NT, hrows.data() + NT, NT * sizeof(double));
+      if (Gamma) std::memcpy(Gamma + (size_t)dst * NT, hrows.data(), NT * sizeof(double));
+      if (alphaTilde) std::memcpy(alphaTilde + (size_t)dst * NT, hrows.data() + NT, NT * sizeof(double));
       if (alpha) {
-        double *A = alpha + (size_t)i * NT * NT;
+        double *A = alpha + (size_t)dst * NT * NT;
         std::memset(A, 0, (size_t)NT * NT * sizeof(double));
         if (c->G.non_resonant) {
           for (int b = 1; b < NT; ++b)
@@ -900,15 +1045,18 @@ int nusi_tables_batch(nusi_ctx *c, int n, const double *mphi, const double *g, c
     }
   }
   if (rc == NUSI_OK && status) {
-    cudaError_t e = cudaMemcpy(status, p->d_status0, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost);
+    cudaError_t e = cudaMemcpy(hst.data(), p->d_statw, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) rc = fail(NUSI_E_CUDA, cudaGetErrorString(e));
+    for (int i = 0; i < n && rc == NUSI_OK; ++i) status[p->reordered ? p->h_out_index[i] : i] = hst[i];
   }
   nusi_points_destroy(p);
   return rc;
 }
 
-int nusi_last_timing(const nusi_ctx *c, float *ms_rows, float *ms_alpha, float *ms_integrate, int *n_launches) {
+int nusi_last_timing(const nusi_ctx *cc, float *ms_rows, float *ms_alpha, float *ms_integrate, int *n_launches) {
+  nusi_ctx *c = const_cast<nusi_ctx *>(cc);
   if (!c) return NUSI_E_INVALID;
+  std::lock_guard<std::mutex> lk(c->mu);
   float tr = 0, ta = 0, ti = 0;
   for (int i = 0; i + 5 < c->ev_used && i + 5 < (int)c->ev.size(); i += 6) {
     CU(cudaEventSynchronize(c->ev[i + 5]));
@@ -977,9 +1125,8 @@ static int generate_table(int which, const char *path, const std::vector<double>
   for (long long first = 0; first < total && e == cudaSuccess && io_ok; first += slab) {
     const long long cnt = std::min(slab, total - first);
     cudaEventRecord(e0);
-    phiphi_table_kernel<<<(unsigned)((cnt + 127) / 128), 128>>>(which, first, cnt, (int)n1, (int)n2, d_x[0], d_x[1], d_x[2], d_out);
+    e = launch_phiphi_table(which, first, cnt, (int)n1, (int)n2, d_x[0], d_x[1], d_x[2], d_out);
     cudaEventRecord(e1);
-    e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpy(vals.data(), d_out, (size_t)cnt * sizeof(float), cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) break;
     float ms = 0;
@@ -1038,7 +1185,7 @@ int nusi_phiphi_tables_generate(int device, const char *alphatilde_path, const c
 }
 
 int nusi_specfun_eval(int device, int which, int n, const double *x, const double *y, double *re, double *im) {
-  if (n <= 0 || !x || !re || which < 0 || which > 3 || (which == 1 && (!y || !im))) return NUSI_E_INVALID;
+  if (n <= 0 || !x || !re || which < 0 || which > 7 || (which == 1 && (!y || !im)) || (which == 6 && !y)) return NUSI_E_INVALID;
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
     return fail(NUSI_E_NO_DEVICE, "no CUDA device");
@@ -1048,8 +1195,7 @@ int nusi_specfun_eval(int device, int which, int n, const double *x, const doubl
   for (int i = 0; i < 4; ++i) CU(cudaMalloc((void **)&d[i], b));
   CU(cudaMemcpy(d[0], x, b, cudaMemcpyHostToDevice));
   if (y) CU(cudaMemcpy(d[1], y, b, cudaMemcpyHostToDevice));
-  specfun_kernel<<<(n + 127) / 128, 128>>>(which, n, d[0], d[1], d[2], d[3]);
-  CU(cudaGetLastError());
+  CU(launch_specfun(which, n, d[0], d[1], d[2], d[3]));
   CU(cudaMemcpy(re, d[2], b, cudaMemcpyDeviceToHost));
   if (im && which == 1) CU(cudaMemcpy(im, d[3], b, cudaMemcpyDeviceToHost));
   for (int i = 0; i < 4; ++i) cudaFree(d[i]);
@@ -1073,7 +1219,7 @@ int nusi_measure_fp64_peak(int device, double *tflops) {
   double best = 0;
   for (int rep = 0; rep < 4; ++rep) {
     CU(cudaEventRecord(e0));
-    fp64_peak_kernel<<<blocks, thr>>>(d, iters, 0.999999, 1e-9);
+    CU(launch_fp64_peak(blocks, thr, d, iters));
     CU(cudaEventRecord(e1));
     CU(cudaEventSynchronize(e1));
     float ms = 0;

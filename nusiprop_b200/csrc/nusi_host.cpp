@@ -147,6 +147,42 @@ double freestream_energy(double zmax_eff, double lEmin, double lEmax, double si,
   return gl3_panels(0, zmax_eff, [&](double z) { return lum_times_E(z) / cosmo_H(z); });
 }
 
+// nuSIprop.hpp:638-646, expression for expression (log(exp(-x) + 1), not log1p; pow-free prefactor handed in)
+static double dsnb_lum_int(double pref, double z, double E) {
+  const double Tnue = 6e6;
+  return pref * (-E * E * (1 + z) * std::log(std::exp(-E * (1 + z) / Tnue) + 1) / Tnue + 2 * E * li2_neg(-std::exp(-E * (1 + z) / Tnue)) +
+                 2 * Tnue * li3_neg(-std::exp(-E * (1 + z) / Tnue)) / (1 + z));
+}
+void dsnb_source(int N, int S, const double *zsrc, const double *rsn, double pref, const double *Emin, const double *Emax, double *out) {
+  for (int i = 0; i < S; ++i)
+    for (int j = 0; j < N; ++j)
+      out[(size_t)i * N + j] = (dsnb_lum_int(pref, zsrc[i], Emax[j]) - dsnb_lum_int(pref, zsrc[i], Emin[j])) * rsn[i];
+}
+
+// E_FS of the supernova source: sum_i L^i(z, E(1+z)) = 3 R_SN(z) dN/dE(E(1+z)) (nuSIprop.hpp:607-626: the derivative of
+// Lum_int with respect to E is dN/dE(E(1+z)) R_SN-free), so
+//   E_FS = 3 \int_0^zmax dz R_SN(z)/H(z) \int_Emin^Emax dE E dN/dE(E (1+z)).
+// z: the reference's 100 x 3 Gauss-Legendre panels (:694-729).  E: 3-point Gauss-Legendre on 400 panels uniform in ln E
+// (the integrand E^2 dN/dE d lnE is smooth on that scale: T = 6 MeV against panels 2.9 % wide at 5 decades).
+double freestream_energy_dsnb(double zmax_eff, double lEmin, double lEmax) {
+  const double Etot = 3 * 6.24, Tnue = 6e6;
+  auto dNdE = [&](double E) { return Etot * 120 * std::pow(E, 2) / (6 * 7 * std::pow(M_PI, 4) * std::pow(Tnue, 4) * (std::exp(E / Tnue) + 1)); };
+  const double la = lEmin * std::log(10.0), lb = lEmax * std::log(10.0);
+  auto e_integral = [&](double z) {
+    const int n_panels = 400;
+    double res = 0;
+    for (int f = 0; f < n_panels; ++f) {
+      const double a = la + f * (lb - la) / n_panels, b = la + (f + 1.0) * (lb - la) / n_panels;
+      for (int q = 0; q < 3; ++q) {
+        const double E = std::exp((b - a) / 2. * gl_x(q) + (b + a) / 2.);
+        res += (b - a) / 2. * gl_w(q) * E * E * dNdE(E * (1 + z));  // dE E f = dlnE E^2 f
+      }
+    }
+    return res;
+  };
+  return gl3_panels(0, zmax_eff, [&](double z) { return 3.0 * cosmo_RSN(z) * e_integral(z) / cosmo_H(z); });
+}
+
 double scalar_width(double mphi, double g, bool majorana) {
   if (majorana) return sqr(g) * mphi / (16.0 * M_PI);
   return sqr(g) * mphi / (8.0 * M_PI);

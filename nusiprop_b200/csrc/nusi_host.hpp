@@ -40,6 +40,11 @@ double scalar_width(double mphi, double g, bool majorana);
 void powerlaw_source(int N, int S, const double *zsrc, const double *Emin, const double *Emax, double zmax_eff, double si,
                      double norm, double *out);
 double freestream_energy(double zmax_eff, double lEmin, double lEmax, double si, double norm);
+// This fork's source, Lum(z_i, bin j) = (Lum_int(z, Ep) - Lum_int(z, Em)) R_SN(z)  (nuSIprop.hpp:638-662), with the same
+// glibc calls and the same Li2 / Li3 evaluation as the reference build: out[i * N + j], i < S.
+void dsnb_source(int N, int S, const double *zsrc, const double *rsn, double pref, const double *Emin, const double *Emax, double *out);
+// counterpart of energy_FS() (nuSIprop.hpp:694-729) for that source: \int dz/H \int dE E sum_i L^i(z, E(1+z))
+double freestream_energy_dsnb(double zmax_eff, double lEmin, double lEmax);
 
 // phi-phi tables: binary loader (interp.hpp:249-292) + contraction of the log10(delta) axis.
 struct HostPhiPhi {

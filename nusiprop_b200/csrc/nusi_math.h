@@ -27,7 +27,7 @@
 
 #if defined(__CUDACC__)
 #define NUSI_HD __host__ __device__ __forceinline__
-#define NUSI_HD_NOINLINE __host__ __device__ __noinline__
+#define NUSI_HD_NOINLINE static __host__ __device__ __noinline__
 #else
 #define NUSI_HD inline
 #define NUSI_HD_NOINLINE inline
@@ -39,9 +39,9 @@ namespace nusi {
 // per call site otherwise, and the builder kernels have ~60 call sites: the instruction cache is
 // the first bottleneck of this path).  On the host they are the libm calls.
 #if defined(__CUDA_ARCH__)
-__device__ __noinline__ double nlog(double x) { return ::log(x); }
-__device__ __noinline__ double nlog1p(double x) { return ::log1p(x); }
-__device__ __noinline__ double natan2(double y, double x) { return ::atan2(y, x); }
+static __device__ __noinline__ double nlog(double x) { return ::log(x); }
+static __device__ __noinline__ double nlog1p(double x) { return ::log1p(x); }
+static __device__ __noinline__ double natan2(double y, double x) { return ::atan2(y, x); }
 #else
 inline double nlog(double x) { return ::log(x); }
 inline double nlog1p(double x) { return ::log1p(x); }
@@ -117,14 +117,14 @@ NUSI_HD cplx ccub(cplx a) { return a * a * a; }
 #define NUSI_BERN_LIST NUSI_BERN_1, NUSI_BERN_2, NUSI_BERN_3, NUSI_BERN_4, NUSI_BERN_5, NUSI_BERN_6, NUSI_BERN_7, NUSI_BERN_8, \
                        NUSI_BERN_9, NUSI_BERN_10, NUSI_BERN_11, NUSI_BERN_12, NUSI_BERN_13
 #if defined(__CUDACC__)
-__device__ __constant__ double nusi_bern_dev[13] = {NUSI_BERN_LIST};
+static __device__ __constant__ double nusi_bern_dev[13] = {NUSI_BERN_LIST};
 #endif
 static const double nusi_bern_host[13] = {NUSI_BERN_LIST};
 // (-1)^(n+1)/n, n = 2..17: Taylor coefficients of log(1+x) beyond the linear term
 #define NUSI_LOGC_LIST -1.0 / 2, 1.0 / 3, -1.0 / 4, 1.0 / 5, -1.0 / 6, 1.0 / 7, -1.0 / 8, 1.0 / 9, -1.0 / 10, 1.0 / 11, -1.0 / 12, \
                        1.0 / 13, -1.0 / 14, 1.0 / 15, -1.0 / 16, 1.0 / 17
 #if defined(__CUDACC__)
-__device__ __constant__ double nusi_logc_dev[16] = {NUSI_LOGC_LIST};
+static __device__ __constant__ double nusi_logc_dev[16] = {NUSI_LOGC_LIST};
 #endif
 static const double nusi_logc_host[16] = {NUSI_LOGC_LIST};
 namespace nusi {
@@ -289,8 +289,8 @@ NUSI_HD_NOINLINE cplx cli2(double x, double y) {
 }  // namespace nusi
 
 #if defined(__CUDACC__)
-__device__ __constant__ double nusi_li2_cheb_dev[NUSI_POLYLOG_NCHEB] = {NUSI_LI2_CHEB};
-__device__ __constant__ double nusi_li3_cheb_dev[NUSI_POLYLOG_NCHEB] = {NUSI_LI3_CHEB};
+static __device__ __constant__ double nusi_li2_cheb_dev[NUSI_POLYLOG_NCHEB] = {NUSI_LI2_CHEB};
+static __device__ __constant__ double nusi_li3_cheb_dev[NUSI_POLYLOG_NCHEB] = {NUSI_LI3_CHEB};
 #endif
 static const double nusi_li2_cheb_host[NUSI_POLYLOG_NCHEB] = {NUSI_LI2_CHEB};
 static const double nusi_li3_cheb_host[NUSI_POLYLOG_NCHEB] = {NUSI_LI3_CHEB};

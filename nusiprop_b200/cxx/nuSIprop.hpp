@@ -10,7 +10,9 @@
 //     g++ -std=c++11 -O2 -I nusiprop_b200/cxx -I include test.cpp -L nusiprop_b200/lib -lnusiprop_b200
 //
 // Differences a user can observe (all deliberate):
-//   * objects with the same fixed options share one GPU context (grids, source term, phi-phi tables);
+//   * objects with the same fixed options share one GPU context (grids, source term, phi-phi tables); the library
+//     serialises calls on one context and the registry of contexts is locked, so one object per thread (an OpenMP
+//     loop over a scan, as with the reference) is safe -- though evolve_scan() below is the fast way to do that;
 //     it is created at the first evolve() -- or in the constructor when non_resonant && phiphi, where
 //     the reference loads its tables and exit(1)s if a file is missing (interp.hpp:251-254);
 //   * fatal conditions print the reference's message and exit(1) like the reference, unless
@@ -29,6 +31,7 @@
 #include <iostream>
 #include <map>
 #include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <tuple>
@@ -52,16 +55,20 @@ inline void fatal(const std::string &msg) {
 // one GPU context per distinct set of fixed options, shared by all objects that use it
 struct ctx_handle {
   nusi_ctx *c = nullptr;
+  std::mutex mu;  // held across "set the power-law source, then evolve" (source_model 1: si and norm are per object)
   explicit ctx_handle(nusi_ctx *c_) : c(c_) {}
   ~ctx_handle() { nusi_ctx_destroy(c); }
   ctx_handle(const ctx_handle &) = delete;
   ctx_handle &operator=(const ctx_handle &) = delete;
 };
-// fixed options ..., device, then the source: (source_model, si, norm); si and norm are 0 for source_model 0 (inert there)
-typedef std::tuple<bool, bool, bool, int, double, double, double, int, bool, int, int, double, double> ctx_key;
+// fixed options ..., device, source_model.  si and norm are not part of the key: with source_model 1 evolve() re-uploads
+// the power-law table of the shared context when they differ (nusi_ctx_set_powerlaw), so sampling si creates no contexts.
+typedef std::tuple<bool, bool, bool, int, double, double, double, int, bool, int, int> ctx_key;
 
-inline std::shared_ptr<ctx_handle> acquire_ctx(const ctx_key &key) {
+inline std::shared_ptr<ctx_handle> acquire_ctx(const ctx_key &key, double si = 2.0, double norm = 1.0) {
   static std::map<ctx_key, std::weak_ptr<ctx_handle>> registry;
+  static std::mutex registry_mu;
+  std::lock_guard<std::mutex> lk(registry_mu);
   std::shared_ptr<ctx_handle> h = registry[key].lock();
   if (h) return h;
   nusi_opts o;
@@ -78,8 +85,8 @@ inline std::shared_ptr<ctx_handle> acquire_ctx(const ctx_key &key) {
   o.device = std::get<9>(key);
   o.source_model = std::get<10>(key);
   if (o.source_model == 1) {
-    o.si = std::get<11>(key);
-    o.norm = std::get<12>(key);
+    o.si = si;
+    o.norm = norm;
   }
   nusi_ctx *c = nullptr;
   const int rc = nusi_ctx_create(&c, &o);
@@ -121,8 +128,7 @@ class calculate_flux {
       detail::fatal("nuSIprop (B200): invalid binning options");
     // the reference loads the phi-phi tables here and exits if they are missing (:166-170)
     if (non_resonant && phiphi) {
-      ctx_key_in_use = key();
-      ctx = detail::acquire_ctx(ctx_key_in_use);
+      ctx = detail::acquire_ctx(key(), si, norm);
     }
   }
 
@@ -130,15 +136,18 @@ class calculate_flux {
   double mphi, g, mntot, si, norm;
 
   void evolve() {
-    // (re-)acquire: with source_model 1 the context depends on the public, modifiable si and norm
-    if (!ctx || key() != ctx_key_in_use) {
-      ctx_key_in_use = key();
-      ctx = detail::acquire_ctx(ctx_key_in_use);
-    }
+    if (!ctx) ctx = detail::acquire_ctx(key(), si, norm);
     if (!ctx) return;
     std::vector<double> fm(3 * (size_t)N_bins_E), ff(3 * (size_t)N_bins_E);
     status = 0;
-    const int rc = nusi_evolve_batch(ctx->c, 1, &mphi, &g, &mntot, fm.data(), ff.data(), &status);
+    int rc;
+    if (source_model == 1) {  // si and norm are public, modifiable members: the shared context gets this object's source first
+      std::lock_guard<std::mutex> lk(ctx->mu);
+      rc = nusi_ctx_set_powerlaw(ctx->c, si, norm);
+      if (rc == NUSI_OK) rc = nusi_evolve_batch(ctx->c, 1, &mphi, &g, &mntot, fm.data(), ff.data(), &status);
+    } else {
+      rc = nusi_evolve_batch(ctx->c, 1, &mphi, &g, &mntot, fm.data(), ff.data(), &status);
+    }
     if (rc != NUSI_OK) {
       detail::fatal(std::string("nuSIprop (B200): evolve failed: ") + nusi_strerror(rc) + " (" + nusi_last_error() + ")");
       return;
@@ -167,6 +176,20 @@ class calculate_flux {
     double E_FS = 0;
     nusi_freestream_energy(zmax, lEmin, lEmax, si, norm, &E_FS);
     evolve();
+    double E_int = 0;
+    for (int i = 0; i < N_bins_E; ++i)
+      for (int k = 0; k < 3; ++k) E_int += (std::log(Emax[i]) - std::log(Emin[i])) * (E_nu[i] * E_nu[i]) * flux[k][i];
+    return (E_int - E_FS) / E_FS;
+  }
+
+  /* extra (not in the reference): the same ratio with E_FS the free-streaming energy of the source that is really
+   * injected (this fork's supernova background for source_model 0), nusi_ctx_freestream_energy: what
+   * check_energy_conservation() is meant to measure.  The reference's own number above is -1 in the fork's default mode. */
+  double check_energy_conservation_consistent(void) {
+    evolve();
+    if (!ctx) return 0;
+    double E_FS = 0;
+    nusi_ctx_freestream_energy(ctx->c, &E_FS);
     double E_int = 0;
     for (int i = 0; i < N_bins_E; ++i)
       for (int k = 0; k < 3; ++k) E_int += (std::log(Emax[i]) - std::log(Emin[i])) * (E_nu[i] * E_nu[i]) * flux[k][i];
@@ -213,11 +236,10 @@ class calculate_flux {
   std::vector<std::vector<double>> flux, flux_fla;  // [3][N_bins_E]; copied with the object
   std::vector<double> E_nu, Emin, Emax;
   std::shared_ptr<detail::ctx_handle> ctx;  // shared, never copied
-  detail::ctx_key ctx_key_in_use;
 
   detail::ctx_key key() const {
     return detail::ctx_key(majorana, non_resonant, normal_ordering, N_bins_E, lEmin, lEmax, zmax_arg, flav, phiphi, device,
-                           source_model, source_model == 1 ? si : 0.0, source_model == 1 ? norm : 0.0);
+                           source_model);
   }
   bool index_ok(const char *what, int i, int j) const {
     if ((i < 0) || (i >= 3)) {
@@ -244,7 +266,7 @@ inline int evolve_scan(int n, const double *mphi, const double *g, const double 
                        int N_bins_E = 300, double lEmin = 12.0, double lEmax = 17.0, double zmax = 5.0, int flav = 2,
                        bool phiphi = false) {
   std::shared_ptr<detail::ctx_handle> h = detail::acquire_ctx(detail::ctx_key(
-      majorana, non_resonant, normal_ordering, N_bins_E, lEmin, lEmax, zmax, flav, phiphi, detail::default_device(), 0, 0.0, 0.0));
+      majorana, non_resonant, normal_ordering, N_bins_E, lEmin, lEmax, zmax, flav, phiphi, detail::default_device(), 0));
   if (!h) return NUSI_E_NO_DEVICE;
   return nusi_evolve_batch(h->c, n, mphi, g, mntot, flux_mass, flux_fla, status);
 }

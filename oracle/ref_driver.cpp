@@ -38,10 +38,13 @@
 #include "polylogarithm/src/cpp/Li3.hpp"
 #include <complex.h>
 #include <stdint.h>
+#ifndef NUSI_REF_ULP_SEED
+#define NUSI_REF_ULP_SEED 0  // other seeds = other members of the ensemble (which quarter of the values moves, and which way)
+#endif
 static inline double nusi_ulp(double v) {
   uint64_t b;
   std::memcpy(&b, &v, 8);
-  uint64_t h = b * 0x9E3779B97F4A7C15ull;
+  uint64_t h = (b ^ ((uint64_t)NUSI_REF_ULP_SEED * 0xD6E8FEB86659FD93ull)) * 0x9E3779B97F4A7C15ull;
   h ^= h >> 29;
   const unsigned r = (unsigned)(h >> 40) & 7u;
   if (r == 0) return nextafter(v, INFINITY);

@@ -3,7 +3,9 @@
 // library is built under tests/ and is never loaded by the nusiprop_b200 package.
 #include "nusi_math.h"
 #ifdef NUSI_HOSTCHECK_XSEC
-#include "nusi_xsec.h"
+#include "nusi_gamma.h"
+#include "nusi_alphatilde.h"
+#include "nusi_alpha.h"
 #endif
 
 extern "C" {

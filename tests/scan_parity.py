@@ -1,0 +1,81 @@
+"""Parity criterion of the HEADLINE workload (BASELINE configs[4], the 256 x 256 (mphi, g) scan at N_E = 200) against
+tests/golden/oracle_scan1024.npz -- the strict oracle and its 6-member noise-floor ensemble on the seeded 1024-point
+subsample (tools/gen_scan_golden.py).  Test infrastructure: used by tests/test_scan_parity.py and by bench.py's
+"parity" key; never by the product.
+
+A (point, bin) pair passes if   |cuda - oracle| / |oracle|  <=  max(1e-9, K * floor(point, bin)),   K = 4, where
+floor(point, bin) is the largest deviation of any ensemble member (the SAME reference sources rebuilt with FMA
+contraction, or with +-1 ulp on a quarter of their libm results) from the strict oracle IN THAT BIN -- no widening
+over neighbouring bins.  Reported tiers:
+    strict_frac   pairs within 1e-9 (north_star's tolerance), to be compared with ref_strict_frac = how often one
+                  rebuild of the reference agrees with the strict one to 1e-9 (best single member)
+    floor_frac    pairs within max(1e-9, K floor); n_excused = pairs that needed the floor term
+"""
+import os
+
+import numpy as np
+
+FIXTURE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "oracle_scan1024.npz")
+K_FLOOR = 4.0
+STRICT = 1e-9
+
+
+def load_fixture():
+    z = np.load(FIXTURE)
+    return {k: z[k] for k in z.files}
+
+
+def relerr(a, b):
+    with np.errstate(all="ignore"):
+        r = np.abs(a - b) / np.abs(b)
+    r[a == b] = 0.0
+    r[np.isnan(a) & np.isnan(b)] = 0.0
+    r[np.isnan(r)] = np.inf
+    return r
+
+
+def evaluate(got_mass, fx=None, k=K_FLOOR):
+    """got_mass [P][3][N]: mass-basis fluxes of the fixture's points (fixture order).  Returns the tier report."""
+    fx = fx or load_fixture()
+    ref, floor = fx["mass"], fx["floor"].astype(np.float64)
+    r = relerr(np.asarray(got_mass, dtype=np.float64), ref).max(axis=1)  # [P][N], worst of the three mass eigenstates
+    tol = np.maximum(STRICT, k * floor)
+    ratio = r / tol
+    p, b = np.unravel_index(int(np.argmax(ratio)), ratio.shape)
+    pw, bw = np.unravel_index(int(np.argmax(np.where(np.isfinite(r), r, -1))), r.shape)
+    return {
+        "points": int(ref.shape[0]), "bins": int(ref.shape[0] * ref.shape[2]), "k_floor": k,
+        "strict_frac": float(np.mean(r <= STRICT)),
+        "ref_strict_frac": float(np.max(fx["member_strict_frac"])),
+        "floor_frac": float(np.mean(r <= tol)),
+        "n_excused": int(np.sum((r > STRICT) & (r <= tol))),
+        "n_failed": int(np.sum(r > tol)),
+        "worst_rel": float(r[pw, bw]), "worst_rel_floor": float(floor[pw, bw]),
+        "worst_point": {"mphi": float(fx["mphi"][pw]), "g": float(fx["g"][pw]), "bin": int(bw)},
+        "worst_over_tol": float(ratio[p, b]),
+        "worst_over_tol_point": {"mphi": float(fx["mphi"][p]), "g": float(fx["g"][p]), "bin": int(b), "rel": float(r[p, b]), "floor": float(floor[p, b])},
+    }
+
+
+def evolve_fixture_points_in_their_shards(ctx, fx=None, mntot=0.1, n_shards=8):
+    """Evolve the WHOLE scan, shard by shard in scan order through ctx.evolve (so that the grouped scan kernels produce
+    the numbers exactly as in the benchmarked workload), and return the fixture points' mass fluxes, their status words
+    and the grouping of the last shard."""
+    fx = fx or load_fixture()
+    idx = fx["index"].astype(np.int64)
+    i, j = np.meshgrid(np.arange(256), np.arange(256), indexing="ij")
+    mphi = (10.0 ** (1.0 + 3.0 * i / 255.0)).ravel()
+    g = (10.0 ** (-5.0 + 5.0 * j / 255.0)).ravel()
+    assert np.array_equal(mphi[idx], fx["mphi"]) and np.array_equal(g[idx], fx["g"])
+    out = np.zeros_like(fx["mass"])
+    st = np.zeros(len(idx), dtype=np.int32)
+    info = None
+    for r in range(n_shards):
+        sel = np.arange(r, mphi.size, n_shards)
+        fm, ff, s = ctx.evolve(mphi[sel], g[sel], mntot)
+        info = ctx.last_grouping()
+        mine = np.nonzero(idx % n_shards == r)[0]
+        out[mine] = fm[idx[mine] // n_shards]
+        st[mine] = s[idx[mine] // n_shards]
+        assert np.isfinite(fm).all() and np.isfinite(ff).all(), "non-finite flux in shard %d" % r
+    return out, st, info

@@ -78,13 +78,22 @@ def test_source_term_device_kernel(nusi):
     """Lum(z_i, bin j) from the CUDA source kernel (device exp/log + Li2/Li3) vs the oracle's.  The
     difference of antiderivatives cancels ~1e8-fold in the two lowest bins (E << T), so those carry
     the libm difference amplified; everywhere else the device values equal glibc's to the last bits."""
-    ctx = nusi.Context(**CFG200)
+    ctx = nusi.Context(source_device=1, **CFG200)
     s = ctx.source()
     ref = np.load(os.path.join(GOLD, "oracle_source_N200.npz"))["source"]
     r = relerr(s, ref)
     assert r[:, 4:].max() < 1e-9
     assert np.mean(r == 0.0) > 0.95  # device exp/log reproduce glibc's bits almost everywhere
     assert r.max() < 1e-6
+    ctx.close()
+
+
+def test_source_term_default_is_the_reference_array_bitwise(nusi):
+    """Default: Lum(z_i, bin j) is computed on the host with the reference's own arithmetic (same glibc calls, same
+    Li2 / Li3 evaluation) and uploaded, so the integrator's source is the oracle's array bit for bit."""
+    ctx = nusi.Context(**CFG200)
+    ref = np.load(os.path.join(GOLD, "oracle_source_N200.npz"))["source"]
+    assert np.array_equal(ctx.source(), ref)
     ctx.close()
 
 
@@ -203,77 +212,59 @@ def _scan_sample(n, seed=0):
 
 
 def test_wave_integrator_equals_serial_integrator_bitwise(nusi):
-    """The bin-owned wavefront kernel and the reference-shaped bin-by-bin kernel produce the same bits (same
-    accumulation order per cell).  The default integrator (diagonal-owned sums) also keeps that order; it forms
-    the two quotients of a cell as reciprocal x numerator + one FMA correction, which is the correctly rounded
+    """The bin-owned wavefront kernel (opts.integrator = 1) and the reference-shaped bin-by-bin kernel (2) produce the
+    same bits (same accumulation order per cell).  The default integrator (diagonal-owned sums) also keeps that order;
+    it forms the two quotients of a cell as reciprocal x numerator + one FMA correction, which is the correctly rounded
     quotient except for all-ones divisors and subnormal results: it must agree to a few ulp at most."""
     mphi, g = _scan_sample(48, 5)
     for cfg in (dict(majorana=1, **CFG200), dict(majorana=0, **CFG200), dict(N_bins_E=240, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2),
                 dict(N_bins_E=97, lEmin=5.0, lEmax=8.0, zmax=2.0, flav=1)):
-        ctx = nusi.Context(**cfg)
-        os.environ.pop("NUSI_SERIAL_INTEGRATOR", None)
-        a = ctx.evolve(mphi, g, 0.1)
-        os.environ["NUSI_SERIAL_INTEGRATOR"] = "1"
-        try:
-            b = ctx.evolve(mphi, g, 0.1)
-        finally:
-            os.environ.pop("NUSI_SERIAL_INTEGRATOR", None)
-        os.environ["NUSI_WAVE_INTEGRATOR"] = "1"
-        try:
-            c = ctx.evolve(mphi, g, 0.1)
-        finally:
-            os.environ.pop("NUSI_WAVE_INTEGRATOR", None)
+        res = []
+        for integ in (0, 2, 1):
+            ctx = nusi.Context(integrator=integ, **cfg)
+            res.append(ctx.evolve(mphi, g, 0.1))
+            ctx.close()
+        a, b, c = res
         assert np.array_equal(b[0], c[0], equal_nan=True) and np.array_equal(b[1], c[1], equal_nan=True), cfg
         assert np.array_equal(np.isnan(a[0]), np.isnan(b[0])), cfg
         ok = ~np.isnan(b[0])
         assert np.all(np.abs(a[0][ok] - b[0][ok]) <= 1e-14 * np.abs(b[0][ok]) + 1e-300), cfg
         print("default vs serial integrator: %.4f of the values bit-identical" % np.mean(a[0][ok] == b[0][ok]))
-        ctx.close()
     # several bands and several bins / diagonals per thread (N_E = 500: BPT 2, SB 16, DPT 3) vs the bin-owned kernel
-    ctx = nusi.Context(N_bins_E=500, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
+    cfg = dict(N_bins_E=500, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
+    ctx = nusi.Context(**cfg)
     a = ctx.evolve(mphi[:3], g[:3], 0.1)
-    os.environ["NUSI_WAVE_INTEGRATOR"] = "1"
-    try:
-        c = ctx.evolve(mphi[:3], g[:3], 0.1)
-    finally:
-        os.environ.pop("NUSI_WAVE_INTEGRATOR", None)
+    ctx.close()
+    ctx = nusi.Context(integrator=1, **cfg)
+    c = ctx.evolve(mphi[:3], g[:3], 0.1)
+    ctx.close()
     ok = ~np.isnan(c[0])
     assert np.array_equal(np.isnan(a[0]), np.isnan(c[0])) and np.all(np.abs(a[0][ok] - c[0][ok]) <= 1e-14 * np.abs(c[0][ok]) + 1e-300)
-    ctx.close()
 
 
 @pytest.mark.parametrize("N_E", [300, 900, 1100])
 def test_wide_integrator_configurations_equal_wave_kernel(nusi, N_E):
     """Finer binning runs 512 threads per point (N_E = 300, the class default: BPT 1, SB 32; 900: BPT 2, SB 16, DPT 3;
     1100: BPT 4, SB 8, DPT 4, as N_E = 2000).  Same accumulation order as the bin-owned wave kernel and as the
-    256-thread configurations (NUSI_FINE_VARIANT=0)."""
+    256-thread configurations (opts.fine_variant = 1)."""
     mphi, g = _scan_sample(3, 11)
-    ctx = nusi.Context(N_bins_E=N_E, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
-    a = ctx.evolve(mphi, g, 0.1)
-    try:
-        os.environ["NUSI_WAVE_INTEGRATOR"] = "1"
-        c = ctx.evolve(mphi, g, 0.1)
-        os.environ.pop("NUSI_WAVE_INTEGRATOR", None)
-        os.environ["NUSI_FINE_VARIANT"] = "0"
-        b = ctx.evolve(mphi, g, 0.1)
-    finally:
-        os.environ.pop("NUSI_WAVE_INTEGRATOR", None)
-        os.environ.pop("NUSI_FINE_VARIANT", None)
+    cfg = dict(N_bins_E=N_E, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
+    res = []
+    for kw in (dict(), dict(fine_variant=1), dict(integrator=1)):
+        ctx = nusi.Context(**cfg, **kw)
+        res.append(ctx.evolve(mphi, g, 0.1))
+        ctx.close()
+    a, b, c = res
     ok = ~np.isnan(c[0])
     assert ok.any() and np.array_equal(np.isnan(a[0]), np.isnan(c[0]))
     assert np.array_equal(a[0], b[0], equal_nan=True) and np.array_equal(a[1], b[1], equal_nan=True)
     assert np.all(np.abs(a[0][ok] - c[0][ok]) <= 1e-14 * np.abs(c[0][ok]) + 1e-300)
-    ctx.close()
 
 
 def test_tiled_builder_equals_per_entry_builder_bitwise(nusi):
     """elementary_mode 0: the tiled kernel (shared vertices) must produce the per-entry kernel's bits."""
     mphi, g = _scan_sample(6, 7)
-    os.environ["NUSI_NO_TILES"] = "1"
-    try:
-        c0 = nusi.Context(elementary_mode=0, **CFG200)
-    finally:
-        os.environ.pop("NUSI_NO_TILES")
+    c0 = nusi.Context(elementary_mode=0, builder_per_entry=1, **CFG200)
     c1 = nusi.Context(elementary_mode=0, **CFG200)
     t0, t1 = c0.tables(mphi, g, 0.1), c1.tables(mphi, g, 0.1)
     assert np.array_equal(t0[2], t1[2], equal_nan=True) and np.array_equal(t0[0], t1[0]) and np.array_equal(t0[1], t1[1])
@@ -286,11 +277,7 @@ def test_compact_builder_equals_per_entry_evaluation_bitwise(nusi):
     formulas evaluated entry by entry -- a check of the tiling / edge bookkeeping, independent of parity."""
     mphi, g = _scan_sample(6, 9)
     for cfg in (CFG200, dict(N_bins_E=47, lEmin=5.0, lEmax=8.0, zmax=3.0, flav=0), dict(N_bins_E=300, lEmin=12.0, lEmax=17.0, zmax=5.0, flav=2)):
-        os.environ["NUSI_NO_TILES"] = "1"
-        try:
-            c0 = nusi.Context(elementary_mode=2, **cfg)
-        finally:
-            os.environ.pop("NUSI_NO_TILES")
+        c0 = nusi.Context(elementary_mode=2, builder_per_entry=1, **cfg)
         c1 = nusi.Context(elementary_mode=2, **cfg)
         t0, t1 = c0.tables(mphi, g, 0.1), c1.tables(mphi, g, 0.1)
         assert np.array_equal(t0[2], t1[2], equal_nan=True), cfg
@@ -330,25 +317,83 @@ def test_scan_builder_equals_compact_builder_bitwise(nusi):
 def test_scan_builder_race_stress(nusi):
     """compute-sanitizer is not available on the GPU pool, so the pipelined shared-memory hand-offs of the scan kernels
     (double-buffered G, triple-buffered cp.async fields, one barrier per point) are stressed instead: a full 2048-point
-    slice plus a ragged tail, every group length 1..32 cut by NUSI_GROUP_MAX, repeated, each run compared bit for bit
+    slice plus a ragged tail, every group length 1..32 cut by opts.group_max, repeated, each run compared bit for bit
     with the compact builder (which has no per-point pipeline)."""
     M, Gg = np.meshgrid(10 ** np.linspace(1, 4, 75), 10 ** np.linspace(-5, 0, 33), indexing="ij")
     mphi, g = M.ravel(), Gg.ravel()
     c2 = nusi.Context(elementary_mode=2, **CFG200)
     ref = c2.evolve(mphi, g, 0.1)
     c2.close()
-    c3 = nusi.Context(elementary_mode=3, **CFG200)
-    try:
-        for gm in (32, 2, 3, 5, 7, 11, 16, 31, 32, 32):
-            os.environ["NUSI_GROUP_MAX"] = str(gm)
-            os.environ["NUSI_GROUP_ALWAYS"] = "1"
-            got = c3.evolve(mphi, g, 0.1)
-            for a, b in zip(ref, got):
-                assert np.array_equal(a, b, equal_nan=True), gm
-    finally:
-        os.environ.pop("NUSI_GROUP_MAX", None)
-        os.environ.pop("NUSI_GROUP_ALWAYS", None)
+    for gm in (32, 2, 3, 5, 7, 11, 16, 31, 32, 32):
+        c3 = nusi.Context(elementary_mode=3, group_max=gm, group_always=1, **CFG200)
+        got = c3.evolve(mphi, g, 0.1)
         c3.close()
+        for a, b in zip(ref, got):
+            assert np.array_equal(a, b, equal_nan=True), gm
+
+
+def test_regrouping_makes_the_scan_builder_independent_of_the_callers_order(nusi):
+    """The batch is sorted by (mphi, m_nu) on the host before the groups are cut and the results are scattered back,
+    so a g-major grid and a shuffled scan get the scan builder too -- and the same bits as the mphi-major order
+    (opts.keep_order = 1 is the unsorted path: groups of one, compact builder)."""
+    M, Gg = np.meshgrid(10 ** np.linspace(1, 4, 40), 10 ** np.linspace(-5, 0, 32), indexing="ij")
+    mphi, g = M.ravel(), Gg.ravel()
+    mnt = np.where(np.arange(mphi.size) % 7 == 0, 0.15, 0.1)  # two mass sums inside every row
+    ctx = nusi.Context(**CFG200)
+    ctx.evolve(mphi, g, 0.1)
+    assert not ctx.last_grouping()["reordered"]  # an mphi-major grid with one mass sum is already in evolve order
+    ref = ctx.evolve(mphi, g, mnt)
+    perm = np.random.default_rng(3).permutation(mphi.size)
+    gmaj = np.arange(mphi.size).reshape(40, 32).T.ravel()
+    for order in (perm, gmaj):
+        got = ctx.evolve(mphi[order], g[order], mnt[order])
+        info = ctx.last_grouping()
+        assert info["reordered"] and info["n_grouped_points"] >= 0.9 * mphi.size, info
+        for a, b in zip(ref, got):
+            assert np.array_equal(a[order], b, equal_nan=True)
+    # device-resident path with a reordered batch
+    import torch
+    dev = torch.device("cuda", 0)
+    pts = ctx.upload_points(mphi[perm], g[perm], mnt[perm])
+    fm = torch.empty((mphi.size, 3, 200), dtype=torch.float64, device=dev)
+    ff = torch.empty_like(fm)
+    st = torch.full((mphi.size,), -1, dtype=torch.int32, device=dev)
+    ctx.evolve_points(pts, fm.data_ptr(), ff.data_ptr(), st.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert np.array_equal(fm.cpu().numpy(), ref[0][perm], equal_nan=True) and np.array_equal(st.cpu().numpy(), ref[2][perm])
+    pts.close()
+    ctx.close()
+    ck = nusi.Context(keep_order=1, **CFG200)
+    got = ck.evolve(mphi[perm], g[perm], mnt[perm])
+    assert not ck.last_grouping()["reordered"]
+    for a, b in zip(ref, got):
+        assert np.array_equal(a[perm], b, equal_nan=True)
+    ck.close()
+
+
+def test_non_finite_parameters_are_rejected_per_point(nusi):
+    """NaN / inf / non-positive parameters never reach the mass cache or the kernels: the point gets
+    NUSI_ST_BAD_PARAM (| NO_MASS for mntot) and NaN fluxes, its neighbours are untouched -- NaN first and NaN in the
+    middle of a batch (a NaN key used to poison the std::map the masses were cached in)."""
+    ctx = nusi.Context(**CFG200)
+    good = ctx.evolve([100.0, 30.0], [1e-2, 1e-1], [0.1, 0.1])
+    nan = float("nan")
+    for pos in (0, 1):
+        mphi, g, mn = [100.0, 30.0], [1e-2, 1e-1], [0.1, 0.1]
+        for which, bits in ((mn, 256 | 512), (g, 512), (mphi, 512)):
+            arrs = [list(mphi), list(g), list(mn)]
+            tgt = arrs[[mphi, g, mn].index(which)]
+            tgt.insert(pos, nan)
+            for a in arrs:
+                if a is not tgt:
+                    a.insert(pos, a[0])
+            fm, ff, st = ctx.evolve(*arrs)
+            assert st[pos] == bits and np.isnan(fm[pos]).all() and np.isnan(ff[pos]).all()
+            keep = [i for i in range(3) if i != pos]
+            assert np.array_equal(fm[keep], good[0]) and np.array_equal(st[keep], good[2])
+    fm, ff, st = ctx.evolve([float("inf"), -5.0, 0.0], [1e-2] * 3, [0.1] * 3)
+    assert np.all(st == 512) and np.isnan(fm).all()
+    ctx.close()
 
 
 def test_batch_invariance_and_permutation(nusi):

@@ -1,0 +1,69 @@
+"""BASELINE configs[4] under a parity gate: the 256 x 256 (mphi, g) scan at N_E = 200, evolved shard by shard in
+scan order with the DEFAULT builder (elementary_mode 3: alpha_group_kernel / rows_group_kernel on groups of 32), against
+the oracle on the seeded 1024-point subsample (reference path nuSIprop.hpp:176-337).  Criterion and tiers:
+tests/scan_parity.py."""
+import numpy as np
+import pytest
+
+import scan_parity as SP
+
+CFG200 = dict(majorana=True, non_resonant=True, normal_ordering=True, N_bins_E=200, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
+
+
+def test_fixture_is_the_oracle(oracle):
+    """The committed fixture is what the oracle (and its ensemble) produce here, now: a few points live (not gpu)."""
+    fx = SP.load_fixture()
+    assert fx["mass"].shape == (1024, 3, 200) and fx["floor"].shape == (1024, 200) and len(set(fx["index"].tolist())) == 1024
+    assert np.array_equal(fx["index"], np.random.default_rng(20261104).choice(65536, 1024, replace=False))
+    for p in (0, 511, 1023):
+        fm = oracle.evolve(float(fx["mphi"][p]), float(fx["g"][p]), 0.1, **CFG200)[0]
+        assert np.array_equal(fm, fx["mass"][p])
+        dev = np.zeros(200)
+        for v in fx["members"]:
+            dev = np.maximum(dev, oracle.relerr(oracle.evolve(float(fx["mphi"][p]), float(fx["g"][p]), 0.1, variant=str(v), **CFG200)[0], fm).max(axis=0))
+        assert np.array_equal(dev.astype(np.float32), fx["floor"][p])
+    # the corners of the scan the advisor asked about are inside the sample's range
+    assert fx["mphi"].min() < 12 and fx["mphi"].max() > 9e3 and fx["g"].max() > 0.9 and fx["g"].min() < 1.1e-5
+
+
+def test_criterion_rejects_a_wrong_result():
+    """The gate is not vacuous: a relative perturbation of 1e-8 in well-conditioned bins fails it."""
+    fx = SP.load_fixture()
+    ok = SP.evaluate(fx["mass"], fx)
+    assert ok["n_failed"] == 0 and ok["strict_frac"] == 1.0
+    bad = fx["mass"].copy()
+    p, b = np.unravel_index(np.argmin(fx["floor"] + (fx["mass"][:, 0, :] == 0)), fx["floor"].shape)
+    bad[p, :, b] *= 1 + 1e-8
+    rep = SP.evaluate(bad, fx)
+    assert rep["n_failed"] == 1 and rep["worst_over_tol"] > 5
+
+
+@pytest.mark.gpu
+def test_headline_scan_matches_the_oracle_in_scan_order_with_the_default_builder(nusi):
+    fx = SP.load_fixture()
+    ctx = nusi.Context(**CFG200)
+    got, st, info = SP.evolve_fixture_points_in_their_shards(ctx, fx)
+    ctx.close()
+    # the grouped scan kernels really produced these numbers: every shard is 256 groups of 32 points, in the caller's order
+    assert info == dict(n_groups=256, n_grouped_points=8192, reordered=False), info
+    assert np.all(st & ~7 == 0)
+    rep = SP.evaluate(got, fx)
+    print("scan parity:", rep)
+    # every bin within max(1e-9, 4 x the reference's own spread in THAT bin) -- no widening over neighbouring bins
+    assert rep["n_failed"] == 0, rep
+    # and within 1e-9 at least as often as a rebuild of the reference agrees with the reference
+    assert rep["strict_frac"] >= rep["ref_strict_frac"], rep
+    assert rep["strict_frac"] > 0.92
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", [0, 2])
+def test_headline_sample_other_builders(nusi, mode):
+    """The strict builder (mode 0) and the compact builder (mode 2, = mode 3 bit for bit) on the same sample."""
+    fx = SP.load_fixture()
+    ctx = nusi.Context(elementary_mode=mode, **CFG200)
+    fm, ff, st = ctx.evolve(fx["mphi"], fx["g"], 0.1)
+    ctx.close()
+    rep = SP.evaluate(fm, fx)
+    print("mode", mode, rep)
+    assert rep["n_failed"] == 0 and rep["strict_frac"] >= rep["ref_strict_frac"], rep
