@@ -10,10 +10,14 @@ scan, with fewer GPUs it is the first N shards (weak scaling, fixed per-GPU work
 
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
     python bench.py --impl reference --gpus N --steps K ...   # the reference's own CPU evolve()
+    python bench.py --workload fine [--points P]              # BASELINE configs[3]: N_E = 2000 (not the headline line)
 
-One JSON line on stdout (rank 0).  `value` times the device-resident path (inputs already in HBM,
-outputs left in HBM); `e2e` times nusi_evolve_batch through the C ABI with HOST buffers (H2D of
-the parameters and D2H of both flux arrays inside the timed region).
+One JSON line on stdout (rank 0).  `value` times the device-resident path of the product's scan API
+(nusiprop_b200.scan.ScanRunner: inputs already in HBM, outputs left in HBM, gather to rank 0 with N > 1); `e2e`
+times nusi_evolve_batch through the C ABI with HOST buffers (H2D of the parameters and D2H of both flux arrays
+inside the timed region).  At N = 1 the line also carries `parity` -- the whole scan evolved in the same run and
+compared with the oracle fixture of the seeded 1024-point subsample (tests/scan_parity.py) -- `roofline` (executed
+FP64 flops of each kernel / the DFMA peak measured in the same run) and `cpu_baseline`.
 """
 import argparse
 import json
@@ -119,7 +123,7 @@ def ref_binary():
     return None
 
 
-def run_reference_sample(points, cores):
+def run_reference_sample(points, cores, n_e=N_E):
     """Run evolve() for `points` [(mphi, g)] with `cores` concurrent single-point processes.
     Returns wall seconds."""
     exe = ref_binary()
@@ -135,7 +139,7 @@ def run_reference_sample(points, cores):
                     mphi, g = next(it)
                 except StopIteration:
                     return
-            subprocess.run([exe, "evolve", repr(float(mphi)), repr(float(g)), repr(MNTOT), "2", "1", "1", "1", "1", str(N_E),
+            subprocess.run([exe, "evolve", repr(float(mphi)), repr(float(g)), repr(MNTOT), "2", "1", "1", "1", "1", str(n_e),
                             repr(LEMIN), repr(LEMAX), repr(ZMAX), str(FLAV), "0", "1", "1"],
                            stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, check=True)
 
@@ -155,30 +159,53 @@ def cpu_sample_points(count):
     return [(mphi[i], g[i]) for i in idx]
 
 
+FINE_N_E = 2000
+FINE_POINTS = [(100.0, 1e-2), (100.0, 1e-1), (30.0, 1e-2), (300.0, 1e-1)]  # first one = BASELINE configs[3] / SURVEY S-fine
+
+
 def bench_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     cores = os.cpu_count() or 1
-    per_step = max(cores * 2, 16)  # ~2 evolve() per core per step, ~0.35 s each
-    for _ in range(args.warmup):
-        run_reference_sample(cpu_sample_points(min(cores, 16)), cores)
+    fine = args.workload == "fine"
+    if fine:  # one N_E = 2000 evolve() takes ~34 s on one core: one point per core per step
+        per_step = min(cores, len(FINE_POINTS))
+        pts = lambda cnt: (FINE_POINTS * ((cnt + len(FINE_POINTS) - 1) // len(FINE_POINTS)))[:cnt]
+        n_e = FINE_N_E
+        for _ in range(min(args.warmup, 1)):
+            run_reference_sample(pts(per_step), cores, n_e)
+    else:
+        per_step = max(cores * 2, 16)  # ~2 evolve() per core per step, ~0.35 s each
+        pts = cpu_sample_points
+        n_e = N_E
+        for _ in range(args.warmup):
+            run_reference_sample(pts(min(cores, 16)), cores, n_e)
     t = 0.0
-    for s in range(args.steps):
-        t += run_reference_sample(cpu_sample_points(per_step), cores)
-    value = per_step * args.steps / t
-    sample = "%d evolve() per step (seeded subsample of the 256x256 scan), one process per point, %d concurrent" % (per_step, cores)
+    steps = min(args.steps, 2) if fine else args.steps
+    for s in range(steps):
+        t += run_reference_sample(pts(per_step), cores, n_e)
+    value = per_step * steps / t
+    sample = "%d evolve() per step (%s), one process per point, %d concurrent" % (
+        per_step, "N_E=2000 points" if fine else "seeded subsample of the 256x256 scan", cores)
     line = {
-        "metric": "(mphi,g) evolutions/sec at N_E=200", "value": value, "unit": "evolutions/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
+        "metric": "(mphi,g) evolutions/sec at N_E=%d" % n_e, "value": value, "unit": "evolutions/s", "n_gpus": args.gpus,
+        "steps": steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "impl": "reference",
-        "config": workload_config(args.gpus),
+        "config": fine_config(per_step) if fine else workload_config(args.gpus),
         "cpu_baseline": {"value": value, "unit": "evolutions/s", "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": "evolutions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
     return 0
+
+
+def fine_config(points):
+    return {"workload": "S-fine (BASELINE configs[3]): N_E=2000, lE 4->9 (N_z=313, NT=2311), zmax=5, Majorana, non_resonant, NO, flav=2, "
+                        "phiphi off, mntot=0.1; %d point(s) per step" % points,
+            "points_per_gpu_per_step": points, "N_bins_E": FINE_N_E,
+            "l2": "per-point alpha table 21.4 MB; the batch's tables exceed L2 from 6 points on"}
 
 
 def workload_config(gpus):
@@ -188,44 +215,70 @@ def workload_config(gpus):
             "l2": "per-step working set (packed alpha tables, 1.7 GB per GPU) exceeds the 126 MB L2; no flush needed"}
 
 
-def roofline(nb, device, flops_table_per_point, points, steps, ms_alpha_total):
-    """The dominant kernel (alpha table builder; alpha_group_kernel on a scan) against the FP64 pipe.
-    achieved = SURVEY 8(d) census (13.9 kflop per table entry of the reference's per-entry formulation) x entries
-    x points / CUDA-event time of the kernel, measured live.  The kernel shares vertex work between entries and
-    g-independent work between the points of a (mphi, m_nu) group, so it EXECUTES far fewer flops than the census
-    counts: frac is "reference-equivalent work per second / peak" and exceeds 1.  What the pipe really does is in
-    executed_tflops / executed_frac (FP64 flops the kernel executes per point, from the committed ncu capture:
-    2 x DFMA + DMUL + DADD thread instructions, x points / live kernel time, / live DFMA peak) and fp64_pipe_pct
-    (ncu sm__pipe_fp64_cycles_active of the same capture).  traffic = ncu dram bytes read + written, scaled from
-    the captured launch to this launch's point count."""
-    peak = nb.measure_fp64_peak(device)
-    ach = (flops_table_per_point * points * steps) / (ms_alpha_total * 1e-3) / 1e12 if ms_alpha_total > 0 else None
-    r = {"bound": "fp64", "kernel": "alpha_group_kernel", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
-         "frac": (ach / peak) if ach else None, "traffic": None, "fp64_pipe_pct": None, "executed_tflops": None, "executed_frac": None,
-         "note": "peak = DFMA rate measured in this run (MEASURED_PEAKS.json has no FP64 figure); achieved = algorithmic census "
-                 "(13.9 kflop x NT(NT-1)/2 entries x points) / CUDA-event kernel time, i.e. reference-equivalent work: the kernel "
-                 "executes far fewer flops (vertices shared between entries, g-independent work shared between the points of a "
-                 "scan row), so frac > 1; executed_tflops / executed_frac / fp64_pipe_pct are what the FP64 pipe really does"}
+def roofline(peak, points, steps, ms_kernel, pipeline_slice=2048):
+    """Each kernel of the step against the FP64 pipe -- the binding resource (arithmetic intensity ~4e4
+    flop/B against a ridge of ~6; no contraction anywhere, so tensor cores have nothing to do).
+      achieved  = FP64 flops the kernel EXECUTES per point (2 x DFMA + DMUL + DADD thread instructions of the committed
+                  ncu capture of the same launch shape, profiles/ncu_roofline.json) x points / CUDA-event time measured
+                  live in this run;   peak = DFMA rate measured in this run (MEASURED_PEAKS.json has no FP64 figure);
+      frac      = achieved / peak.  fp64_pipe_pct = ncu sm__pipe_fp64_cycles_active of the capture (pipe utilisation:
+                  higher than frac because only part of the FP64 instructions are FMAs -- contraction is off for parity).
+      reference_equivalent_x = SURVEY 8(d)'s per-entry census of the REFERENCE's formulation (13.9 kflop per table entry)
+                  / the same time / peak: how much reference work per second the step replaces, NOT a utilisation
+                  (the kernels share vertex work between entries and g-independent work between the points of a scan row).
+      traffic   = ncu dram bytes read + written per launch of one 2048-point pipeline slice."""
+    out = {"bound": "fp64", "kernel": "alpha_group_kernel", "achieved": None, "peak": peak, "unit": "TFLOP/s", "frac": None,
+           "traffic": None, "peak_source": "DFMA rate measured in this run by nusi_measure_fp64_peak (8 independent chains per thread)"}
     try:
-        k = json.load(open(os.path.join(ROOT, "profiles", "ncu_roofline.json")))["alpha_group_kernel"]
-        r["traffic"] = (k["dram_bytes_read"] + k["dram_bytes_write"]) / k["points_in_capture"] * points
-        r["fp64_pipe_pct"] = k["fp64_pipe_pct"]
-        if k.get("fp64_flop") and ms_alpha_total > 0:
-            r["executed_tflops"] = k["fp64_flop"] / k["points_in_capture"] * points * steps / (ms_alpha_total * 1e-3) / 1e12
-            r["executed_frac"] = r["executed_tflops"] / peak
-        r["ncu_source"] = k["source"]
-    except Exception:
-        pass
-    return r
+        prof = json.load(open(os.path.join(ROOT, "profiles", "ncu_roofline.json")))
+    except Exception as ex:
+        out["note"] = "profiles/ncu_roofline.json unavailable: %s" % ex
+        return out, 0.0, 0.0, 0.0
+    fam = {"alpha_kernel": ["alpha_group_kernel", "edges_kernel"], "integrate_kernel": ["integrate_diag_kernel"],
+           "rows_kernel": ["rows_group_kernel<0>", "rows_group_kernel<1>"]}
+    kernels, tot_flop, tot_busy, tot_ms = {}, 0.0, 0.0, 0.0
+    for key, names in fam.items():
+        ms = ms_kernel.get(key, 0.0)
+        for nm in names:
+            k = prof.get(nm)
+            if not k:
+                continue
+            flop_pp = k["fp64_flop"] / k["points_in_capture"]
+            share = k["duration_ms"] / sum(prof[n]["duration_ms"] for n in names if n in prof)  # this kernel's share of the family's event time
+            t = ms * share
+            e = {"ms_per_step": t / steps, "executed_mflop_per_point": flop_pp / 1e6, "fp64_pipe_pct": k["fp64_pipe_pct"],
+                 "achieved": flop_pp * points * steps / (t * 1e-3) / 1e12 if t > 0 else None,
+                 "dram_bytes_per_slice": (k["dram_bytes_read"] + k["dram_bytes_write"]) * pipeline_slice / k["points_in_capture"],
+                 "ncu_source": k["source"]}
+            e["frac"] = e["achieved"] / peak if e["achieved"] else None
+            kernels[nm] = e
+            tot_flop += flop_pp * points * steps
+            tot_busy += t * k["fp64_pipe_pct"] / 100.0
+            tot_ms += t
+    out["kernels"] = kernels
+    d = kernels.get("alpha_group_kernel")
+    if d:
+        out.update(achieved=d["achieved"], frac=d["frac"], traffic=d["dram_bytes_per_slice"], fp64_pipe_pct=d["fp64_pipe_pct"],
+                   ncu_source=d["ncu_source"])
+    return out, tot_flop, tot_busy, tot_ms
+
+
+def validate_outputs(fm, ff, st, what):
+    """The timed workload must be a real result: every status word clean up to the reference's own warnings, every flux finite."""
+    bad = int(np.sum((st & ~7) != 0))
+    if bad or not np.isfinite(fm).all() or not np.isfinite(ff).all():
+        raise RuntimeError("%s: %d points with a fatal status, finite mass %s, finite flavour %s" % (what, bad, np.isfinite(fm).all(), np.isfinite(ff).all()))
+    return {"points": int(st.size), "status_clean": int(np.sum(st == 0)), "status_warn_only": int(np.sum((st != 0) & ((st & ~7) == 0))), "all_finite": True}
 
 
 # ---------------------------------------------------------------------------------------------
-# CUDA arm
+# CUDA arm, headline workload
 # ---------------------------------------------------------------------------------------------
 def bench_cuda(args):
     import torch
     import torch.distributed as dist
     import nusiprop_b200 as nb
+    from nusiprop_b200.scan import ScanRunner
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -238,22 +291,17 @@ def bench_cuda(args):
 
     ctx = nb.Context(majorana=True, non_resonant=True, normal_ordering=True, N_bins_E=N_E, lEmin=LEMIN, lEmax=LEMAX, zmax=ZMAX,
                      flav=FLAV, phiphi=False, device=local)
-    mphi, g = shard(rank % N_SHARDS)
+    # weak scaling: N GPUs evolve the first N shards of the scan, one 8192-point shard each.  The product's scan API
+    # shards a point list p -> rank p mod world, so hand it the interleaved union of those shards.
+    mphi_all, g_all = scan_points()
+    sel = np.arange(mphi_all.size).reshape(-1, N_SHARDS)[:, :world].ravel()  # points of shards 0..world-1, interleaved
     if args.points:
-        mphi, g = mphi[: args.points], g[: args.points]
-    n = mphi.size
+        sel = sel[: args.points * world]
+    run = ScanRunner(ctx, mphi_all[sel], g_all[sel], MNTOT)
+    n = run.n_local
+    mphi, g = mphi_all[sel][run.idx], g_all[sel][run.idx]
+    assert np.array_equal(mphi, shard(rank % N_SHARDS)[0][:n])
     mntot = np.full(n, MNTOT)
-    pts = ctx.upload_points(mphi, g, mntot)
-    fm = torch.empty((n, 3, N_E), dtype=torch.float64, device=dev)
-    ff = torch.empty_like(fm)
-    st = torch.zeros(n, dtype=torch.int32, device=dev)
-    gathered = [torch.empty_like(ff) for _ in range(world)] if (world > 1 and rank == 0) else None
-    stream = torch.cuda.current_stream().cuda_stream
-
-    def step():
-        ctx.evolve_points(pts, fm.data_ptr(), ff.data_ptr(), st.data_ptr(), stream)
-        if world > 1:  # the scan's only exchange: final gather of the flavour fluxes to rank 0
-            dist.gather(ff, gathered, dst=0)
 
     def barrier():
         if world > 1:
@@ -261,30 +309,31 @@ def bench_cuda(args):
         torch.cuda.synchronize()
 
     for _ in range(max(args.warmup, 0)):
-        step()
+        run.step()
     barrier()
+    ctx.last_timing()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    t_rows = t_alpha = t_int = 0.0
-    launches = 0
     e0.record()
     for _ in range(args.steps):
-        step()
-        tm = ctx.last_timing()  # blocks on this step's events (no effect on device time)
-        t_rows += tm["ms_rows"]
-        t_alpha += tm["ms_alpha"]
-        t_int += tm["ms_integrate"]
-        launches += tm["n_launches"]
+        run.step()
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
+    tm = ctx.last_timing()  # per-kernel CUDA-event sums over the timed steps
     if world > 1:
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     clocks = sampler.stop() if rank == 0 else None
+    res = run.result()
+    d_fm, d_ff, d_st = run.flux_mass[:n].cpu().numpy(), run.flux_fla[:n].cpu().numpy(), run.status[:n].cpu().numpy()
+    check = validate_outputs(d_fm, d_ff, d_st, "device-resident path, rank %d" % rank)
+    if world > 1 and rank == 0:  # the gathered scan is what a consumer reads: same numbers as each rank's own
+        assert np.array_equal(res[1][rank::world], d_ff)
+        validate_outputs(res[1], res[1], res[2], "gathered scan")
 
     # end-to-end through the C ABI with host buffers (pinned), every rank concurrently
     h_fm = torch.empty((n, 3, N_E), dtype=torch.float64, pin_memory=True).numpy()
@@ -311,25 +360,48 @@ def bench_cuda(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     # the device path and the host path must agree bit for bit
-    same = bool(np.array_equal(ff.cpu().numpy(), h_ff, equal_nan=True))
+    same = bool(np.array_equal(d_ff, h_ff, equal_nan=True) and np.array_equal(d_fm, h_fm, equal_nan=True) and np.array_equal(d_st, h_st))
+    if not same:
+        raise RuntimeError("host-buffer path and device-resident path disagree")
 
     if rank == 0:
         N, Nz, NT = ctx.N_bins_E, ctx.N_steps_z, ctx.NT
         f_tab, f_rows, f_int = flops_per_evolution(NT, N, Nz)
         total_ev = n * world * args.steps
         value = total_ev / (ms * 1e-3)
+        peak = nb.measure_fp64_peak(local)
+        ms_kernel = {"rows_kernel": tm["ms_rows"], "alpha_kernel": tm["ms_alpha"], "integrate_kernel": tm["ms_integrate"]}
+        rf, tot_flop, tot_busy, tot_ms = roofline(peak, n, args.steps, ms_kernel)
+        if tot_ms > 0:
+            rf["step"] = {"executed_tflops": tot_flop / (ms * 1e-3) / 1e12, "frac": tot_flop / (ms * 1e-3) / 1e12 / peak,
+                          "fp64_pipe_busy_time_weighted": tot_busy / ms, "kernel_ms": tot_ms / args.steps, "ms": ms / args.steps}
+        rf["reference_equivalent_x"] = (f_tab * n * args.steps) / (tm["ms_alpha"] * 1e-3) / 1e12 / peak if tm["ms_alpha"] > 0 else None
         line = {
             "metric": "(mphi,g) evolutions/sec at N_E=200", "value": value, "unit": "evolutions/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(world),
-            "us_per_z_step": 1e3 * t_int / (n * args.steps * (Nz - 1)),
-            "kernel_ms_per_step": {"rows_kernel": t_rows / args.steps, "alpha_kernel": t_alpha / args.steps, "integrate_kernel": t_int / args.steps},
-            "roofline": roofline(nb, local, f_tab, n, args.steps, t_alpha),
+            "us_per_z_step": 1e3 * tm["ms_integrate"] / (n * args.steps * (Nz - 1)),
+            "kernel_ms_per_step": {k: v / args.steps for k, v in ms_kernel.items()},
+            "roofline": rf,
             "e2e": {"value": n * world * e2e_steps / e2e_s, "unit": "evolutions/s", "h2d_bytes_per_step": int(3 * 8 * n),
                     "d2h_bytes_per_step": int(2 * 3 * N * 8 * n + 4 * n), "bitwise_equal_to_device_path": same},
-            "gpu_launches": launches,
+            "gpu_launches": tm["n_launches"],
+            "outputs_checked": check,
             "clocks": clocks,
         }
+        if world == 1 and not args.points:
+            # parity of THIS workload, in this run: the whole scan shard by shard in scan order (default builder), against
+            # the oracle fixture of the seeded 1024-point subsample -- outside the timed region
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            try:
+                import scan_parity as SP
+                got, st, info = SP.evolve_fixture_points_in_their_shards(ctx)
+                rep = SP.evaluate(got)
+                rep["grouping_per_shard"] = info
+                rep["fixture"] = "tests/golden/oracle_scan1024.npz (strict oracle + 6-member ensemble; tools/gen_scan_golden.py)"
+                line["parity"] = rep
+            except Exception as ex:
+                line["parity"] = {"unavailable": str(ex)}
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             cnt = max(cores * 32, 32)
@@ -340,10 +412,84 @@ def bench_cuda(args):
             except Exception as ex:  # oracle binary absent
                 line["cpu_baseline"] = {"value": None, "unit": "evolutions/s", "cores": cores, "kind": "reference", "sample": "unavailable: %s" % ex}
         print(json.dumps(line))
-    pts.close()
+    run.close()
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------
+# CUDA arm, BASELINE configs[3]: fine binning (N_E = 2000).  A side line, not the headline metric.
+# ---------------------------------------------------------------------------------------------
+def bench_fine(args):
+    import torch
+    import nusiprop_b200 as nb
+
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if int(os.environ.get("RANK", "0")) != 0:
+        return 0
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    ctx = nb.Context(majorana=True, non_resonant=True, normal_ordering=True, N_bins_E=FINE_N_E, lEmin=LEMIN, lEmax=LEMAX, zmax=ZMAX,
+                     flav=FLAV, phiphi=False, device=local)
+    N, Nz, NT = ctx.N_bins_E, ctx.N_steps_z, ctx.NT
+    npts = args.points or 148
+    # a small scan: rows of 8 couplings per mediator mass; the first point is BASELINE's (100, 1e-2)
+    nm = (npts + 7) // 8
+    mphi = np.repeat(100.0 * 10 ** (np.arange(nm) * 0.05), 8)[:npts]
+    g = np.tile(1e-2 * 10 ** (np.arange(8) * 0.25), nm)[:npts]
+    mntot = np.full(npts, MNTOT)
+    pts = ctx.upload_points(mphi, g, mntot)
+    fm = torch.empty((npts, 3, N), dtype=torch.float64, device=dev)
+    ff = torch.empty_like(fm)
+    st = torch.zeros(npts, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    steps, warm = max(1, min(args.steps, 3)), max(1, min(args.warmup, 3))
+    for _ in range(warm):
+        ctx.evolve_points(pts, fm.data_ptr(), ff.data_ptr(), st.data_ptr(), stream)
+    torch.cuda.synchronize()
+    ctx.last_timing()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        ctx.evolve_points(pts, fm.data_ptr(), ff.data_ptr(), st.data_ptr(), stream)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    tm = ctx.last_timing()
+    clocks = sampler.stop()
+    check = validate_outputs(fm.cpu().numpy(), ff.cpu().numpy(), st.cpu().numpy(), "fine workload")
+    # one point alone: the latency of a single N_E = 2000 evolve() (what a drop-in calculate_flux::evolve() costs)
+    t0 = time.perf_counter()
+    one = ctx.evolve(100.0, 1e-2, MNTOT)
+    t_first = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    one = ctx.evolve(100.0, 1e-2, MNTOT)
+    t_one = time.perf_counter() - t0
+    tm1 = ctx.last_timing()
+    table_bytes = NT * (NT - 1) / 2 * 8
+    hbm = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs") if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else None
+    int_gbs = table_bytes * npts * steps / (tm["ms_integrate"] * 1e-3) / 1e9 if tm["ms_integrate"] > 0 else None
+    line = {
+        "metric": "(mphi,g) evolutions/sec at N_E=2000", "value": npts * steps / (ms * 1e-3), "unit": "evolutions/s", "n_gpus": 1,
+        "steps": steps, "warmup": warm, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "config": fine_config(npts),
+        "us_per_z_step": 1e3 * tm["ms_integrate"] / (npts * steps * (Nz - 1)),
+        "kernel_ms_per_step": {"rows_kernel": tm["ms_rows"] / steps, "alpha_kernel": tm["ms_alpha"] / steps, "integrate_kernel": tm["ms_integrate"] / steps},
+        "single_point": {"seconds_wall": t_one, "seconds_wall_first_call": t_first, "integrate_ms": tm1["ms_integrate"], "alpha_ms": tm1["ms_alpha"], "rows_ms": tm1["ms_rows"],
+                         "us_per_z_step": 1e3 * tm1["ms_integrate"] / (Nz - 1), "finite": bool(np.isfinite(one[0]).all())},
+        "roofline": {"bound": "hbm", "kernel": "integrate (table streamed once per point)", "achieved": int_gbs, "peak": hbm, "unit": "GB/s",
+                     "frac": (int_gbs / hbm) if (int_gbs and hbm) else None, "traffic": None,
+                     "note": "algorithmic bytes = the packed alpha table (NT(NT-1)/2 doubles = %.1f MB per point) read once by the integrator / its CUDA-event time; "
+                             "peak = MEASURED_PEAKS.json hbm_gbs" % (table_bytes / 1e6)},
+        "gpu_launches": tm["n_launches"], "outputs_checked": check, "clocks": clocks,
+    }
+    print(json.dumps(line))
+    pts.close()
+    ctx.close()
     return 0
 
 
@@ -353,11 +499,14 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="cuda", choices=["cuda", "reference"])
-    ap.add_argument("--points", type=int, default=0, help="debug: evolve only the first POINTS points of the shard")
+    ap.add_argument("--workload", default="scan", choices=["scan", "fine"], help="scan = the headline 256x256 scan at N_E=200; fine = N_E=2000 (configs[3])")
+    ap.add_argument("--points", type=int, default=0, help="debug: evolve only the first POINTS points of the shard (fine: batch size, default 148)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         return bench_reference(args)
+    if args.workload == "fine":
+        return bench_fine(args)
     return bench_cuda(args)
 
 

@@ -80,8 +80,10 @@ typedef struct nusi_opts {
   /* ---- switches of the implementation (ABI 3; all default 0 = the product path).  They select cross-check
    *      kernels and tuning variants that produce the same numbers; tests and tools set them here, nothing in the
    *      library reads the environment. */
-  int integrator;        /* 0 = diagonal-owned wavefront kernel; 1 = bin-owned wavefront kernel (cross-check);
-                            2 = serial, reference-shaped bin-by-bin kernel with true divisions (cross-check, N_bins_E <= 256) */
+  int integrator;        /* 0 = default: role-split wavefront kernel (N_bins_E <= 225), diagonal-owned wavefront kernel above;
+                            1 = bin-owned wavefront kernel (cross-check);
+                            2 = serial, reference-shaped bin-by-bin kernel with true divisions (cross-check, N_bins_E <= 256);
+                            3 = diagonal-owned wavefront kernel at every binning */
   int fine_variant;      /* 0 = 512 threads per point for N_bins_E > 256; 1 = the 256-thread configurations (same bits) */
   int builder_per_entry; /* 1 = no tiling: one thread per table entry (cross-check of the tiled builders) */
   int group_max;         /* most points per scan-builder group; 0 = 32 */
@@ -205,9 +207,9 @@ int nusi_phiphi_tables_generate(int device, const char *alphatilde_path, const c
  * builder: number of groups, points in groups of more than one point, and whether the batch had to be reordered. */
 int nusi_last_grouping(const nusi_ctx *c, int *n_groups, int *n_grouped_points, int *reordered);
 
-/* CUDA-event time of the last nusi_evolve_points / nusi_evolve_batch on this context, per kernel,
- * summed over its launches [ms]: Gamma/alphaTilde rows, alpha table, z-stepping integrator; and
- * how many kernels were launched.  Blocks until that work has finished. */
+/* CUDA-event time of the evolve calls on this context since the previous nusi_last_timing (at most the last 1024
+ * pipeline slices), per kernel, summed over the launches [ms]: Gamma/alphaTilde rows, alpha table, z-stepping
+ * integrator; and how many kernels were launched.  Blocks until that work has finished. */
 int nusi_last_timing(const nusi_ctx *c, float *ms_rows, float *ms_alpha, float *ms_integrate, int *n_launches);
 
 /* Device special functions evaluated on the GPU for n arguments (unit tests of the

@@ -213,7 +213,7 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
   if (o->source_model < 0 || o->source_model > 1 ||
       (o->source_model == 1 && (!(std::fabs(1 - o->si) > 1e-12) || !std::isfinite(o->si) || !std::isfinite(o->norm))))
     return fail(NUSI_E_INVALID, "bad source options (source_model 0 or 1; si != 1 and finite; norm finite)");
-  if (o->integrator < 0 || o->integrator > 2 || o->group_max < 0 || o->rows_split < 0 || o->elementary_mode < 0)
+  if (o->integrator < 0 || o->integrator > 3 || o->group_max < 0 || o->rows_split < 0 || o->elementary_mode < 0)
     return fail(NUSI_E_INVALID, "bad implementation switches");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || o->device < 0 || o->device >= ndev)
@@ -506,7 +506,8 @@ static int ensure_workspace(nusi_ctx *c, int npts) {
   CU(cudaDeviceSynchronize());  // nothing in flight uses the old buffers
   double *rows = nullptr, *tri = nullptr, *work = nullptr, *edges = nullptr;
   cudaError_t e = cudaMalloc((void **)&rows, (size_t)npts * 2 * c->H.NT * sizeof(double));
-  if (e == cudaSuccess) e = cudaMalloc((void **)&tri, (size_t)npts * c->tstride * sizeof(double));
+  // + 16 bytes: the integrator's 16-byte-granular bulk copies may read one double past the last column
+  if (e == cudaSuccess) e = cudaMalloc((void **)&tri, (size_t)npts * c->tstride * sizeof(double) + 16);
   if (e == cudaSuccess && !c->G.non_resonant) e = cudaMalloc((void **)&work, (size_t)npts * 3 * c->H.N * sizeof(double));
   if (e == cudaSuccess && c->use_tiles)
     e = cudaMalloc((void **)&edges, (size_t)npts * edge_block_doubles(c->n_edges, c->H.NT) * sizeof(double));
@@ -612,6 +613,8 @@ static int launch_integrate_stage(nusi_ctx *c, const IntegArgs &A, cudaStream_t 
     e = launch_integrate_serial(A, s);
   else if (c->opt.integrator == 1)
     e = launch_integrate_wave(A, s);
+  else if (c->opt.integrator == 0 && integrate_split_supports(c->G.N, c->G.NT))
+    e = launch_integrate_split(A, s);
   else
     e = launch_integrate_diag(A, c->opt.fine_variant, s);
   if (e == cudaErrorInvalidValue) return fail(NUSI_E_INVALID, "binning not supported by the selected integrator");
@@ -805,8 +808,10 @@ static int run_pipeline(nusi_ctx *c, const nusi_points *p, double *d_fm, double 
   const int SL = c->max_chunk < NUSI_SLICE ? c->max_chunk : NUSI_SLICE;
   const int chunk = p->n <= SL ? p->n : (p->n <= c->max_chunk ? ((p->n + SL - 1) / SL) * SL : std::max(1, c->max_chunk / SL) * SL);
   if ((rc = ensure_workspace(c, chunk))) return rc;
-  c->ev_used = 0;
-  c->n_launches = 0;
+  if (c->ev_used >= 6 * 1024) {  // nobody reads the timings: start over rather than grow for ever
+    c->ev_used = 0;
+    c->n_launches = 0;
+  }
   cudaStream_t sx = overlap ? c->s_x : caller, si = overlap ? c->s_i : caller, sc = to_host ? c->s_copy : caller;
   if (overlap || to_host) {
     CU(cudaEventRecord(c->ev_fork, caller));
@@ -1073,6 +1078,8 @@ int nusi_last_timing(const nusi_ctx *cc, float *ms_rows, float *ms_alpha, float 
   if (ms_alpha) *ms_alpha = ta;
   if (ms_integrate) *ms_integrate = ti;
   if (n_launches) *n_launches = c->n_launches;
+  c->ev_used = 0;  // the next call reports what was launched after this one
+  c->n_launches = 0;
   return NUSI_OK;
 }
 
