@@ -614,7 +614,7 @@ static int launch_integrate_stage(nusi_ctx *c, const IntegArgs &A, cudaStream_t 
   else if (c->opt.integrator == 1)
     e = launch_integrate_wave(A, s);
   else if (c->opt.integrator == 0 && integrate_split_supports(c->G.N, c->G.NT))
-    e = launch_integrate_split(A, s);
+    e = launch_integrate_split(A, c->opt.fine_variant, s);
   else
     e = launch_integrate_diag(A, c->opt.fine_variant, s);
   if (e == cudaErrorInvalidValue) return fail(NUSI_E_INVALID, "binning not supported by the selected integrator");

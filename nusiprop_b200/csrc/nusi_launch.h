@@ -62,7 +62,7 @@ struct IntegArgs {
 cudaError_t launch_integrate_diag(const IntegArgs &A, int fine_variant, cudaStream_t s);
 bool integrate_diag_supports(int N, int NT);
 // k_integrate_split.cu -- product kernel for N_bins_E <= 225: role-split wavefront (critical warp / helpers / bulk warps, TMA ring)
-cudaError_t launch_integrate_split(const IntegArgs &A, cudaStream_t s);
+cudaError_t launch_integrate_split(const IntegArgs &A, int variant, cudaStream_t s);
 bool integrate_split_supports(int N, int NT);
 // k_integrate_check.cu -- bin-owned wavefront, serial reference-shaped, resonant-only
 cudaError_t launch_integrate_wave(const IntegArgs &A, cudaStream_t s);

@@ -12,7 +12,7 @@ rng = np.random.default_rng(5)
 mphi, g = 10 ** rng.uniform(1, 4, 64), 10 ** rng.uniform(-5, 0, 64)
 cfgs = [dict(N_bins_E=200, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2), dict(N_bins_E=200, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2, majorana=0),
         dict(N_bins_E=97, lEmin=5.0, lEmax=8.0, zmax=2.0, flav=1), dict(N_bins_E=120, lEmin=5.0, lEmax=8.5, zmax=3.0, flav=1),
-        dict(N_bins_E=60, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=0), dict(N_bins_E=225, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2),
+        dict(N_bins_E=60, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=0), dict(N_bins_E=224, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2), dict(N_bins_E=33, lEmin=4.0, lEmax=6.0, zmax=5.0, flav=2),
         dict(N_bins_E=100, lEmin=9.0, lEmax=14.0, zmax=5.0, flav=2), dict(N_bins_E=210, lEmin=4.0, lEmax=7.0, zmax=6.0, flav=2)]
 for cfg in cfgs:
     res = {}
@@ -31,10 +31,13 @@ for cfg in cfgs:
         cfg["N_bins_E"], S, cfg.get("majorana", 1), r_ab, r_ac, r_bc, same_nan, np.mean(a[ok] == c[ok]), np.array_equal(res[0][2], res[2][2])), flush=True)
 # timing on the benchmark shard
 m, gg = bench.shard(0)
-for integ in (3, 0):
-    ctx = nb.Context(integrator=integ, N_bins_E=200, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
+ref = None
+for integ, var in ((3, 0), (0, 0), (0, 21), (0, 22), (0, 23), (0, 11), (0, 13)):
+    ctx = nb.Context(integrator=integ, fine_variant=var, N_bins_E=200, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
     for _ in range(3):
         out = ctx.evolve(m, gg, 0.1)
         tm = ctx.last_timing()
-    print("integrator %d: %s finite %s" % (integ, tm, np.isfinite(out[0]).all()), flush=True)
+    if ref is None:
+        ref = out[0]
+    print("integrator %d variant %d: integrate %.3f ms, max rel diff vs diag %.2e" % (integ, var, tm["ms_integrate"], np.max(np.abs(out[0] - ref) / np.abs(ref))), flush=True)
     ctx.close()

@@ -1,34 +1,39 @@
 #!/usr/bin/env python
-"""Aggregate an ncu source page (--page source --csv --print-source cuda,sass) by source file:line."""
-import csv, sys, collections, re
+"""Aggregate an ncu source page by CUDA source line.
+    ncu -i rep --page source --csv --print-source cuda,sass [-k regex:name] > src.csv ; python tools/ncu_source_hot.py src.csv [topn]
+Per line: share of warp-stall samples, warp instructions executed, and the dominant stall reasons."""
+import csv, sys, collections
 path = sys.argv[1]; topn = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 rows = list(csv.reader(open(path)))
-# find header row
-hi = next(i for i, r in enumerate(rows) if r and r[0] == "Line No")
-hdr = rows[hi]
-col = {h: i for i, h in enumerate(hdr)}
-# In cuda,sass mode each SASS row carries the CUDA source line in col "Line No"/"Source"? inspect
-iexec = hdr.index("Instructions Executed"); isamp = hdr.index("# Samples")
-agg = collections.defaultdict(lambda: [0, 0, 0]); src = {}
-cur_file = None
-tot = [0, 0]
+agg = collections.defaultdict(lambda: collections.defaultdict(float)); src = {}
+hdr = None
 for r in rows:
-    if r and r[0] == "File Path": cur_file = r[1].split("/")[-1]; continue
-    if len(r) <= iexec or r[0] in ("Line No", "Function Name"): continue
+    if r and r[0] == "Line No" and len(r) > 5:
+        hdr = r; ci = {h: i for i, h in enumerate(hdr)}; stalls = [h for h in hdr if h.startswith("stall_")]
+        continue
+    if hdr is None or len(r) < len(hdr):
+        continue
     try:
-        ln = r[0]; ex = int(float(r[iexec] or 0)); sm = int(float(r[isamp] or 0))
+        ln = int(r[0])
     except ValueError:
         continue
-    key = (cur_file, ln)
-    agg[key][0] += ex; agg[key][1] += sm; agg[key][2] += 1
-    src.setdefault(key, r[1][:110])
-    tot[0] += ex; tot[1] += sm
-print("total warp-inst %d, samples %d" % tuple(tot))
-byfile = collections.defaultdict(lambda: [0, 0])
-for (f, ln), v in agg.items():
-    byfile[f][0] += v[0]; byfile[f][1] += v[1]
-for f, v in sorted(byfile.items(), key=lambda kv: -kv[1][0]):
-    print("%-28s inst %5.1f%%  samples %5.1f%%" % (f, 100.0 * v[0] / max(tot[0], 1), 100.0 * v[1] / max(tot[1], 1)))
-print()
-for (f, ln), v in sorted(agg.items(), key=lambda kv: -kv[1][0])[:topn]:
-    print("%5.1f%% inst %5.1f%% smp  n_sass=%4d  %s:%s  %s" % (100.0 * v[0] / max(tot[0], 1), 100.0 * v[1] / max(tot[1], 1), v[2], f, ln, src[(f, ln)]))
+    a = agg[ln]
+    for key, col in (("smp", "# Samples"), ("inst", "Instructions Executed")):
+        try: a[key] += float(r[ci[col]] or 0)
+        except ValueError: pass
+    for s in stalls:
+        try: a[s] += float(r[ci[s]] or 0)
+        except ValueError: pass
+    a["nsass"] += 1
+    src.setdefault(ln, r[1][:100])
+ts = sum(a["smp"] for a in agg.values()); ti = sum(a["inst"] for a in agg.values())
+print("total samples %d, warp instructions %d" % (ts, ti))
+tot_st = collections.defaultdict(float)
+for a in agg.values():
+    for k, v in a.items():
+        if k.startswith("stall_"): tot_st[k] += v
+print("stall mix: " + ", ".join("%s %.1f%%" % (k[6:], 100 * v / max(ts, 1)) for k, v in sorted(tot_st.items(), key=lambda kv: -kv[1])[:8]))
+for ln, a in sorted(agg.items(), key=lambda kv: -kv[1]["smp"])[:topn]:
+    st = sorted(((k[6:], v) for k, v in a.items() if k.startswith("stall_") and v > 0), key=lambda kv: -kv[1])[:3]
+    print("%5.1f%% smp %5.1f%% inst n=%3d L%-4d %-70s | %s" % (100 * a["smp"] / max(ts, 1), 100 * a["inst"] / max(ti, 1), a["nsass"], ln, src[ln][:70],
+                                                          " ".join("%s:%.0f%%" % (k, 100 * v / max(a["smp"], 1)) for k, v in st)))
