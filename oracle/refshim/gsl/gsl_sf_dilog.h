@@ -186,7 +186,14 @@ inline cplx c_unitdisk(double x, double y) {
 inline cplx cdilog_xy(double x, double y) {
   const double zeta2 = kPi * kPi / 6.0;
   const double r2 = x * x + y * y;
+  // GSL's rule for an argument exactly on the real axis.  REFSHIM_GSL_REAL_AXIS_FLIP builds the
+  // OTHER sign (the y -> 0+ limit): used only by tests/test_oracle_cpu.py to show that the reference's own positivity
+  // check (nuSIprop.hpp:1505) tells the two conventions apart.
+#ifdef REFSHIM_GSL_REAL_AXIS_FLIP
+  if (y == 0.0) return cplx(dilog(x), (x >= 1.0) ? +kPi * std::log(x) : 0.0);
+#else
   if (y == 0.0) return cplx(dilog(x), (x >= 1.0) ? -kPi * std::log(x) : 0.0);
+#endif
   if (std::fabs(r2 - 1.0) < kEps) return c_bernoulli(x, y);
   if (r2 < 1.0) return c_unitdisk(x, y);
   const double r = std::sqrt(r2);

