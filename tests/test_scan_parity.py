@@ -67,3 +67,23 @@ def test_headline_sample_other_builders(nusi, mode):
     rep = SP.evaluate(fm, fx)
     print("mode", mode, rep)
     assert rep["n_failed"] == 0 and rep["strict_frac"] >= rep["ref_strict_frac"], rep
+
+
+@pytest.mark.gpu
+def test_scan_runner_is_the_product_path_and_equals_context_evolve_bitwise(nusi):
+    """nusiprop_b200.scan.ScanRunner -- what bench.py --gpus N times -- at world size 1: device-resident evolve in
+    2048-point pieces, same bits as one Context.evolve() of the whole shard; evolve_scan_distributed() is built on it."""
+    import bench
+    from nusiprop_b200.scan import ScanRunner, evolve_scan_distributed
+    mphi, g = bench.shard(3)
+    mphi, g = mphi[:5000], g[:5000]  # ragged last piece
+    ctx = nusi.Context(**CFG200)
+    ref = ctx.evolve(mphi, g, 0.1)
+    run = ScanRunner(ctx, mphi, g, 0.1)
+    for _ in range(2):  # a second step reuses the uploaded points and the output tensors
+        fm, ff, st = run.step().result()
+        assert np.array_equal(fm, ref[0]) and np.array_equal(ff, ref[1]) and np.array_equal(st, ref[2])
+    run.close()
+    ctx.close()
+    fm, ff, st = evolve_scan_distributed(mphi[:300], g[:300], 0.1, ctx_kwargs=CFG200)
+    assert np.array_equal(fm, ref[0][:300]) and np.array_equal(ff, ref[1][:300])
