@@ -152,6 +152,16 @@ int nusi_ctx_freestream_energy(nusi_ctx *c, double *E_FS);
  * (d_flux_mass [n][3][N], as nusi_evolve_points leaves them): a device reduction, one double per point into the
  * HOST array E_int[n]. */
 int nusi_energy_integral(nusi_ctx *c, int n, const double *d_flux_mass, double *E_int, void *stream);
+/* nusi_energy_integral() that allocates nothing.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same arguments, same reduction, same bits; the per-point results are staged in a file-scope
+ * `static __device__` array of NUSI_STATIC_MAX_POINTS doubles (512 KiB, held by every GPU that loads the library until
+ * exit) instead of a buffer the context grows with cudaMalloc.  n > NUSI_STATIC_MAX_POINTS returns NUSI_E_INVALID
+ * (nusi_last_error() names the limit).  The array is shared by every call of every context and keeps the last call's
+ * contents (each call overwrites the n slots it reads back; nothing has to start at zero): calls that overlap on the
+ * GPU -- different streams or threads -- race on it.  Calls no cudaMalloc / cudaFree / allocating library routine. */
+#define NUSI_STATIC_MAX_POINTS 65536
+int nusi_energy_integral_static(nusi_ctx *c, int n, const double *d_flux_mass, double *E_int, void *stream);
 
 /* Bin-integrated power-law source of nusi_opts.source_model == 1 -- the upstream Lum() that the reference keeps as a
  * comment (nuSIprop.hpp:648-657) with norm_total = norm / flux_FS_E0() (:205, :666-692) -- for the grids of

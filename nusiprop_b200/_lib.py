@@ -65,6 +65,7 @@ SIGNATURES = {
     "nusi_ctx_set_powerlaw": (C.c_int, [C.c_void_p, C.c_double, C.c_double]),
     "nusi_ctx_freestream_energy": (C.c_int, [C.c_void_p, c_double_p]),
     "nusi_energy_integral": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, c_double_p, C.c_void_p]),
+    "nusi_energy_integral_static": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, c_double_p, C.c_void_p]),
     "nusi_last_grouping": (C.c_int, [C.c_void_p, c_int_p, c_int_p, c_int_p]),
     "nusi_grid": (C.c_int, [C.c_int, C.c_double, C.c_double, C.c_double, c_int_p, c_double_p, c_double_p, c_double_p, c_double_p]),
     "nusi_freestream_energy": (C.c_int, [C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, c_double_p]),

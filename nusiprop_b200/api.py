@@ -152,6 +152,15 @@ class Context(object):
         check(self._lib.nusi_energy_integral(self._h, int(n), C.c_void_p(d_flux_mass), _dp(out), C.c_void_p(stream or None)), "nusi_energy_integral")
         return out
 
+    def energy_integral_static(self, d_flux_mass, n, stream=0, out=None):
+        """energy_integral() through nusi_energy_integral_static: allocates nothing on the device (results staged in the
+        library's file-scope device array, at most NUSI_STATIC_MAX_POINTS = 65536 points; calls that overlap on the GPU
+        race on it).  No counterpart in the reference.  `out`: a caller-owned float64 array [n] to fill."""
+        out = np.zeros(int(n)) if out is None else out
+        check(self._lib.nusi_energy_integral_static(self._h, int(n), C.c_void_p(d_flux_mass), _dp(out), C.c_void_p(stream or None)),
+              "nusi_energy_integral_static")
+        return out
+
     def last_grouping(self):
         a, b, r = C.c_int(), C.c_int(), C.c_int()
         check(self._lib.nusi_last_grouping(self._h, C.byref(a), C.byref(b), C.byref(r)))

@@ -1243,3 +1243,63 @@ int nusi_measure_fp64_peak(int device, double *tflops) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// nusi_energy_integral_static: nusi_energy_integral() for callers that must not allocate (code under CUDA graph capture,
+// serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Same reduction as energy_integral_kernel (k_misc.cu), same bits; the per-point results are staged in a
+// file-scope device array instead of the context's cudaMalloc'ed d_eint, so the call allocates nothing.
+//   * the array is NUSI_STATIC_MAX_POINTS doubles (512 KiB), held by every GPU that loads the library until exit;
+//   * every call (of any context, any thread) shares it: calls that overlap on the GPU race; it keeps the last call's
+//     contents, and nothing needs to start at zero -- each call writes slots [0, n) before it reads them back;
+//   * in host code `g_eint_static` is only a stand-in for the symbol: the device address comes from
+//     cudaGetSymbolAddress, once per device with that device current.
+static __device__ __align__(256) double g_eint_static[NUSI_STATIC_MAX_POINTS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+double *g_eint_static_ptr[kMaxDevices] = {};  // device address of g_eint_static on device d, or NULL
+
+// one warp per point; the arithmetic (and its order) of energy_integral_kernel, k_misc.cu
+__global__ void __launch_bounds__(128) energy_integral_static_kernel(int n, int N, const double *__restrict__ flux_mass,
+                                                                     const double *__restrict__ wE2, double *__restrict__ scratch) {
+  const int p = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (p >= n) return;
+  const double *f = flux_mass + (size_t)p * 3 * N;
+  double acc = 0.0;
+  for (int i = lane; i < N; i += 32) acc += wE2[i] * ((f[i] + f[N + i]) + f[2 * N + i]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) scratch[p] = acc;
+}
+}  // namespace
+
+extern "C" int nusi_energy_integral_static(nusi_ctx *c, int n, const double *d_flux_mass, double *E_int, void *stream) {
+  if (!c || n <= 0 || !d_flux_mass || !E_int) return NUSI_E_INVALID;
+  if (n > NUSI_STATIC_MAX_POINTS)
+    return fail(NUSI_E_INVALID, "nusi_energy_integral_static: n = " + std::to_string(n) + " exceeds NUSI_STATIC_MAX_POINTS = " +
+                                    std::to_string(NUSI_STATIC_MAX_POINTS) + " (use nusi_energy_integral, or split the batch)");
+  std::lock_guard<std::mutex> lk(c->mu);
+  const int dev = c->opt.device;
+  if (dev < 0 || dev >= kMaxDevices) return fail(NUSI_E_INVALID, "nusi_energy_integral_static: device index out of range");
+  CU(cudaSetDevice(dev));
+  double *scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> ls(g_static_mu);
+    if (!g_eint_static_ptr[dev]) {
+      void *p = nullptr;
+      cudaError_t e = cudaGetSymbolAddress(&p, g_eint_static);
+      if (e != cudaSuccess || !p)
+        return fail(NUSI_E_CUDA, std::string("nusi_energy_integral_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+      g_eint_static_ptr[dev] = static_cast<double *>(p);
+    }
+    scratch = g_eint_static_ptr[dev];
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  energy_integral_static_kernel<<<(n + 3) / 4, 128, 0, s>>>(n, c->H.N, d_flux_mass, c->d_wE2, scratch);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(E_int, scratch, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+  return NUSI_OK;
+}
