@@ -80,7 +80,7 @@ typedef struct nusi_opts {
   /* ---- switches of the implementation (ABI 3; all default 0 = the product path).  They select cross-check
    *      kernels and tuning variants that produce the same numbers; tests and tools set them here, nothing in the
    *      library reads the environment. */
-  int integrator;        /* 0 = default: role-split wavefront kernel (N_bins_E <= 225), diagonal-owned wavefront kernel above;
+  int integrator;        /* 0 = default: role-split wavefront kernel (32 <= N_bins_E <= 224), diagonal-owned wavefront kernel above;
                             1 = bin-owned wavefront kernel (cross-check);
                             2 = serial, reference-shaped bin-by-bin kernel with true divisions (cross-check, N_bins_E <= 256);
                             3 = diagonal-owned wavefront kernel at every binning */

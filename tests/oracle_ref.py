@@ -172,6 +172,10 @@ def noise_floor(ref, variants, halfwidth=8):
     return np.array([f[max(0, i - halfwidth): i + halfwidth + 1].max() for i in range(len(f))])
 
 
-def flux_tolerance(ref, variants, k=4.0, strict=1e-9):
-    """north_star's 1e-9 wherever the reference is self-consistent to that level, k x its own spread elsewhere."""
-    return np.maximum(strict, k * noise_floor(ref, variants))
+TOLERANCE_CAP = 0.1  # whatever the ensemble's spread: a flux more than 10 % off the oracle fails
+
+
+def flux_tolerance(ref, variants, k=4.0, strict=1e-9, cap=TOLERANCE_CAP):
+    """north_star's 1e-9 wherever the reference is self-consistent to that level, k x its own spread elsewhere,
+    never more than `cap` (a bin in which the ensemble scatters by O(1) must not excuse an arbitrary result)."""
+    return np.minimum(cap, np.maximum(strict, k * noise_floor(ref, variants)))

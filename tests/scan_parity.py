@@ -3,7 +3,7 @@ tests/golden/oracle_scan1024.npz -- the strict oracle and its 6-member noise-flo
 subsample (tools/gen_scan_golden.py).  Test infrastructure: used by tests/test_scan_parity.py and by bench.py's
 "parity" key; never by the product.
 
-A (point, bin) pair passes if   |cuda - oracle| / |oracle|  <=  max(1e-9, K * floor(point, bin)),   K = 4, where
+A (point, bin) pair passes if   |cuda - oracle| / |oracle|  <=  min(0.1, max(1e-9, K * floor(point, bin))),   K = 4, where
 floor(point, bin) is the largest deviation of any ensemble member (the SAME reference sources rebuilt with FMA
 contraction, or with +-1 ulp on a quarter of their libm results) from the strict oracle IN THAT BIN -- no widening
 over neighbouring bins.  Reported tiers:
@@ -21,6 +21,7 @@ import numpy as np
 
 FIXTURE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "oracle_scan1024.npz")
 K_FLOOR = 4.0
+CAP = 0.1  # whatever the ensemble's spread, a flux more than 10 % off the oracle fails
 STRICT = 1e-9
 
 
@@ -43,7 +44,7 @@ def evaluate(got_mass, fx=None, k=K_FLOOR):
     fx = fx or load_fixture()
     ref, floor = fx["mass"], fx["floor"].astype(np.float64)
     r = relerr(np.asarray(got_mass, dtype=np.float64), ref).max(axis=1)  # [P][N], worst of the three mass eigenstates
-    tol = np.maximum(STRICT, k * floor)
+    tol = np.minimum(CAP, np.maximum(STRICT, k * floor))
     ratio = r / tol
     p, b = np.unravel_index(int(np.argmax(ratio)), ratio.shape)
     pw, bw = np.unravel_index(int(np.argmax(np.where(np.isfinite(r), r, -1))), r.shape)
