@@ -80,10 +80,12 @@ typedef struct nusi_opts {
   /* ---- switches of the implementation (ABI 3; all default 0 = the product path).  They select cross-check
    *      kernels and tuning variants that produce the same numbers; tests and tools set them here, nothing in the
    *      library reads the environment. */
-  int integrator;        /* 0 = default: role-split wavefront kernel (32 <= N_bins_E <= 224), diagonal-owned wavefront kernel above;
+  int integrator;        /* 0 = default: role-split wavefront kernel, one CTA per point (32 <= N_bins_E <= 224) or one point over a
+                                thread-block cluster of 4 CTAs (224 < N_bins_E <= 2017); diagonal-owned wavefront kernel otherwise;
                             1 = bin-owned wavefront kernel (cross-check);
                             2 = serial, reference-shaped bin-by-bin kernel with true divisions (cross-check, N_bins_E <= 256);
-                            3 = diagonal-owned wavefront kernel at every binning */
+                            3 = diagonal-owned wavefront kernel at every binning;
+                            4 = the cluster kernel wherever it applies (N_bins_E > 224), else 3 */
   int fine_variant;      /* 0 = 512 threads per point for N_bins_E > 256; 1 = the 256-thread configurations (same bits) */
   int builder_per_entry; /* 1 = no tiling: one thread per table entry (cross-check of the tiled builders) */
   int group_max;         /* most points per scan-builder group; 0 = 32 */

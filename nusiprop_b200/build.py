@@ -8,7 +8,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 OUT = os.path.join(_HERE, "lib", "libnusiprop_b200.so")
 # Kernel translation units: they are independent of each other, so they compile in parallel.
-SOURCES = ["nusi_capi.cu", "k_rows.cu", "k_alpha.cu", "k_alpha_check.cu", "k_integrate.cu", "k_integrate_split.cu", "k_integrate_check.cu", "k_misc.cu", "k_phiphi.cu",
+SOURCES = ["nusi_capi.cu", "k_rows.cu", "k_alpha.cu", "k_alpha_check.cu", "k_integrate.cu", "k_integrate_split.cu", "k_integrate_cluster.cu", "k_integrate_check.cu", "k_misc.cu", "k_phiphi.cu",
            "nusi_host.cpp"]
 OBJ_DIR = os.path.join(_HERE, "lib", "build")
 FLAGS = [

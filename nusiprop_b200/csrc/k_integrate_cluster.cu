@@ -1,0 +1,528 @@
+// k_integrate_cluster.cu -- the implicit z-stepping integrator (reference nuSIprop.hpp:255-336) for FINE binnings
+// (N_bins_E > 224, BASELINE configs[3]: N_E = 2000): the role-split wavefront of k_integrate_split.cu with ONE POINT
+// SPREAD OVER A THREAD-BLOCK CLUSTER of 4 CTAs (4 SMs).   (sm_100a, FP64 pipe; -fmad=false: contraction only where fma() is written)
+//
+// Why a cluster: the wavefront needs one running sum per (table diagonal, z-step of the band).  At N_E = 2000 that is
+// 2031 diagonals x 32 z-steps x 8 B = 520 KB -- more than one SM's register file, which is why the one-CTA-per-point
+// kernel (integrate_diag_kernel) has to cut the z-axis into 39 bands of 8 z-steps and walk the 2007 waves of a band 39
+// times (78 k dependent waves, 1.9 us each: 0.15 s per point).  Four SMs hold the sums of a 32-step band in registers
+// (508 diagonals per CTA, one per thread), so a point takes 10 bands = 20 k waves, and the wave-to-wave chain is carried
+// by one warp as in integrate_split_kernel instead of by two block-wide barriers per wave.
+//
+//   rank 0, warp 0      critical warp: lane = z-step.  Finalises one cell per lane and wave (flux of the previous z-step by
+//                       warp shuffle, flux-independent half from a helper slot, regeneration sum = far part published by the
+//                       diagonal's owner + the last D = 2B-1 sources kept in registers), and BROADCASTS the new weighted
+//                       flux W of the wave into the shared memory of all four CTAs (st.shared::cluster).
+//   rank 0, warps 1..2  helpers: slots (denominators, reciprocals, source term) one block of B waves ahead.
+//   all ranks, 16 warps bulk: thread u of rank r owns diagonal d = -31 + 508 r + u: acc[s] += T[row(d)][c] W_s for every
+//                       source more than D waves behind its cells, one block behind the critical warp; the owner of the
+//                       diagonal that is finalised in block kb+1 writes its 32 sums into rank 0's shared memory (DSMEM).
+//   every CTA streams ITS slice of each table column (the 508 rows of its diagonals) through a shared-memory ring with
+//   TMA bulk copies (cp.async.bulk + mbarrier), three blocks ahead; rank 0 also fetches the D near-diagonal rows the
+//   critical warp needs.  One cluster barrier (barrier.cluster.arrive.release / wait.acquire) per block of B = 4 waves.
+//
+// Summation order: as integrate_split_kernel -- a cell's regeneration sum is (far part) + (near part), each accumulated
+// in the reference's order (source bins high -> low); it differs from the strictly sequential sum by rounding only.
+#include <cfloat>
+#include "nusi_launch.h"
+#include "nusi_implicit.h"
+#include "nusi_split.h"
+
+namespace nusi {
+
+#define NUSI_CL_C 4      // CTAs per cluster
+#define NUSI_CL_PF 12    // slot fields: lum, offdiag, Gam, aT, Z0, rZ0, Z1, rZ1, Z2, rZ2, dE, 1/dE
+#define NUSI_CL_RB 5     // ring depth in blocks of B columns (block kb-1 .. kb+3)
+#define NUSI_CL_PAD 16   // doubles in front of the near ring: the critical warp reads up to D rows below row 0 of a column
+#define NUSI_CL_NEAR 10  // doubles per near-ring slot: D <= 7 rows + 1 for alignment, rounded to an even count, + 2
+
+__device__ __forceinline__ unsigned cl_rank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ unsigned cl_mapa(unsigned saddr, unsigned rank) {  // the same shared-memory offset in CTA `rank` of the cluster
+  unsigned r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void cl_st_f64(unsigned addr, double v) {
+  asm volatile("st.shared::cluster.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
+__device__ __forceinline__ void cl_st_f64x2(unsigned addr, double a, double b) {
+  asm volatile("st.shared::cluster.v2.f64 [%0], {%1, %2};" ::"r"(addr), "d"(a), "d"(b) : "memory");
+}
+// every thread of every CTA of the cluster; orders the DSMEM stores before it against the loads after it
+__device__ __forceinline__ void cl_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+struct ClCtx {  // at the start of dynamic shared memory of every CTA, filled by its thread 0
+  int N, NT, S, NP, SLOT, DPC, rank;
+  int s0, cnt, n_waves, n_blocks, rowoff, a0;  // a0: table row of this CTA's first diagonal in this band (may be negative)
+  int ring, near, wsh, ash, pre, sdE, sRdE, sCz, sNd, fband, tcoff, fb;  // offsets in doubles
+  unsigned mbar0, ring0, near0, phase0, tpar, wsh_s, ash_s;              // shared::cta byte addresses
+  double U2f[3];
+  const double *T, *source, *rowG, *rowA;
+};
+#define NUSI_CL_CTX_DOUBLES ((int)((sizeof(ClCtx) + 15) / 16) * 2)
+
+struct ClLayout {
+  int SLOT, ring, near, wsh, ash, pre, sdE, sRdE, sCz, sNd, fband, mbar, tcoff, fb, total;
+};
+__host__ __device__ inline ClLayout cl_layout(int N, int S, int B, int DPC) {
+  ClLayout L;
+  L.SLOT = (DPC + 3) & ~1;  // a column slice, possibly shifted by one double for 16-byte alignment of its global source
+  int o = NUSI_CL_CTX_DOUBLES;
+  L.ring = o; o += NUSI_CL_RB * B * L.SLOT;
+  o += NUSI_CL_PAD;
+  L.near = o; o += NUSI_CL_RB * B * NUSI_CL_NEAR;
+  L.wsh = o; o += 2 * B * 32;
+  L.ash = o; o += 2 * B * 32;
+  L.pre = o; o += 2 * B * NUSI_CL_PF * 32;
+  L.sdE = o; o += (N + 1) & ~1;
+  L.sRdE = o; o += (N + 1) & ~1;
+  L.sCz = o; o += (S + 1) & ~1;
+  L.sNd = o; o += (S + 1) & ~1;
+  L.fband = o; o += 3 * ((N + 1) & ~1);
+  L.mbar = o; o += NUSI_CL_RB + 1;
+  L.tcoff = o; o += B;    // 2 x B ints: per wave of a block, where row c of its column sits in the near ring
+  L.fb = o; o += 4 * 32;  // results of the out-of-line general step: f0, f1, f2, W per lane
+  L.total = o;
+  return L;
+}
+
+// packed offset (doubles) of row a of column c, and whether the 16-byte aligned copy that contains it starts one double early
+__device__ __forceinline__ size_t cl_packed(int c, int a) { return (size_t)c * (size_t)(c - 1) / 2 + (size_t)a; }
+__device__ __forceinline__ int cl_mis(unsigned tpar, int c, int a) { return (int)((tpar ^ (unsigned)(c >> 1) ^ (unsigned)a) & 1u); }
+
+__device__ __forceinline__ unsigned cl_parity(unsigned phase0, int kb) {  // parity on which block kb of this band completes
+  const int rb = kb % NUSI_CL_RB;
+  return ((phase0 >> rb) & 1u) ^ (unsigned)((kb / NUSI_CL_RB) & 1);
+}
+
+// One wave of the critical warp (split_wave of k_integrate_split.cu; W goes to all CTAs of the cluster).
+template <int D, bool ALL>
+__device__ __forceinline__ void cl_wave(bool act, int sl, int cnt, int bb, int NP, double U0, double U1, double U2, double czl, double ndl,
+                                        const double *__restrict__ slot, const double *__restrict__ ash, const unsigned (&wdst)[NUSI_CL_C],
+                                        unsigned woff, const double *__restrict__ tc, double *__restrict__ fband, double *__restrict__ fb,
+                                        double (&ip)[D], double &o0, double &o1, double &o2) {
+  const double u0 = __shfl_up_sync(0xffffffffu, o0, 1), u1 = __shfl_up_sync(0xffffffffu, o1, 1), u2 = __shfl_up_sync(0xffffffffu, o2, 1);
+  const double f0 = (sl == 0) ? fband[bb] : u0, f1 = (sl == 0) ? fband[NP + bb] : u1, f2 = (sl == 0) ? fband[2 * NP + bb] : u2;
+  const double lum = slot[0], offdiag = slot[32];
+  const double Z0 = slot[4 * 32], r0 = slot[5 * 32], Z1 = slot[6 * 32], r1 = slot[7 * 32], Z2 = slot[8 * 32], r2 = slot[9 * 32];
+  const double dEb = slot[10 * 32], rdE = slot[11 * 32];
+  const double acc_c = ash[0] + ip[0];
+  const double base = czl * (ndl * acc_c);
+  const double s0 = lum + base * U0, s1 = lum + base * U1, s2 = lum + base * U2;
+  double v0 = quot_fast(f0 + s0, Z0, r0), v1 = quot_fast(f1 + s1, Z1, r1), v2 = quot_fast(f2 + s2, Z2, r2);
+  const double dot = U0 * v0 + U1 * v1 + U2 * v2;
+  double W = quot_fast(dot, dEb, rdE);
+  const int h0 = __double2hiint(v0) & 0x7fffffff, h1 = __double2hiint(v1) & 0x7fffffff, h2 = __double2hiint(v2) & 0x7fffffff;
+  const int hmax = max(h0, max(h1, h2)), hmin = min(h0, min(h1, h2));
+  const bool identity = (hmax < 0x7ff00000) && ((__double2hiint(W) & 0x7fffffff) < 0x7ff00000) &&
+                        (offdiag * __hiloint2double(hmax + 1, 0) <= 6.9388939039072284e-18 /* 2^-57 */ * __hiloint2double(hmin, 0));
+  if (!identity && (ALL || act)) {
+    split_fallback(U0, U1, U2, czl, slot, s0, s1, s2, f0, f1, f2, fb);
+    v0 = fb[0];
+    v1 = fb[32];
+    v2 = fb[64];
+    W = fb[96];
+  }
+  const double Wp = (ALL || act) ? W : 0.0;
+#pragma unroll
+  for (int r = 0; r < NUSI_CL_C; ++r) cl_st_f64(wdst[r] + woff, Wp);
+  if (ALL) {
+    o0 = v0;
+    o1 = v1;
+    o2 = v2;
+#pragma unroll
+    for (int j = 1; j < D; ++j) ip[j - 1] = fma(tc[-j], W, ip[j]);
+    ip[D - 1] = tc[-D] * W;
+  } else {
+    if (act) {
+      o0 = v0;
+      o1 = v1;
+      o2 = v2;
+    }
+#pragma unroll
+    for (int j = 1; j < D; ++j) ip[j - 1] = act ? fma(tc[-j], W, ip[j]) : ip[j];
+    ip[D - 1] = act ? tc[-D] * W : 0.0;
+  }
+  if (sl == cnt - 1 && (ALL || act)) {  // the band's last z-step: this bin's flux after the band
+    fband[bb] = v0;
+    fband[NP + bb] = v1;
+    fband[2 * NP + bb] = v2;
+  }
+}
+
+// ================= critical warp (rank 0) =================
+template <int B>
+static __device__ __noinline__ void cl_critical(double *ssm) {
+  constexpr int D = 2 * B - 1, PF = NUSI_CL_PF;
+  const ClCtx &C = *reinterpret_cast<const ClCtx *>(ssm);
+  const int sl = threadIdx.x & 31, N = C.N, NP = C.NP, cnt = C.cnt, n_blocks = C.n_blocks;
+  const double U0 = C.U2f[0], U1 = C.U2f[1], U2 = C.U2f[2];
+  double *fband = ssm + C.fband, *fb = ssm + C.fb + sl;
+  double ip[D];
+#pragma unroll
+  for (int j = 0; j < D; ++j) ip[j] = 0.0;
+  double o0 = 0.0, o1 = 0.0, o2 = 0.0;
+  const double czl = (sl < cnt) ? ssm[C.sCz + C.S - 1 - C.s0 - sl] : 0.0, ndl = (sl < cnt) ? ssm[C.sNd + C.S - 1 - C.s0 - sl] : 0.0;
+  const unsigned mbar0 = C.mbar0, phase0 = C.phase0;
+  unsigned wdst[NUSI_CL_C];
+#pragma unroll
+  for (int r = 0; r < NUSI_CL_C; ++r) wdst[r] = cl_mapa(C.wsh_s, (unsigned)r) + (unsigned)sl * 8u;
+  for (int kb = 0; kb < n_blocks; ++kb) {
+    mbar_wait(mbar0 + 8u * (kb % NUSI_CL_RB), cl_parity(phase0, kb));
+    const double *slotB = ssm + C.pre + ((kb & 1) * B * PF) * 32 + sl;
+    const double *ashB = ssm + C.ash + (kb & 1) * B * 32 + sl;
+    const unsigned woffB = (unsigned)((kb & 1) * B * 32) * 8u;
+    const int *tco = reinterpret_cast<const int *>(ssm + C.tcoff) + (kb & 1) * B;
+    const int k0 = kb * B - sl;
+    const bool all = (cnt == 32) && (kb * B - 31 >= 0) && (kb * B + B - 1 <= N - 1);
+    if (all) {
+#pragma unroll
+      for (int r = 0; r < B; ++r)
+        cl_wave<D, true>(true, sl, cnt, N - 1 - (k0 + r), NP, U0, U1, U2, czl, ndl, slotB + r * PF * 32, ashB + r * 32, wdst, woffB + (unsigned)(r * 32) * 8u,
+                         ssm + tco[r], fband, fb, ip, o0, o1, o2);
+    } else {
+#pragma unroll
+      for (int r = 0; r < B; ++r) {
+        const int k = k0 + r;
+        const bool act = (sl < cnt) && (k >= 0) && (k <= N - 1);
+        cl_wave<D, false>(act, sl, cnt, act ? N - 1 - k : 0, NP, U0, U1, U2, czl, ndl, slotB + r * PF * 32, ashB + r * 32, wdst, woffB + (unsigned)(r * 32) * 8u,
+                          ssm + tco[r], fband, fb, ip, o0, o1, o2);
+      }
+    }
+    cl_sync();
+  }
+}
+
+// ================= helper warps (rank 0): slots of block kb+1 =================
+template <int B, int NHW>
+__device__ __forceinline__ void cl_help_load(const ClCtx &C, int kb, int hw, int lane, double (&hs)[(B + NHW - 1) / NHW]) {
+  const int zi = max(C.S - 1 - C.s0 - lane, 0);
+#pragma unroll
+  for (int q = 0; q < (B + NHW - 1) / NHW; ++q) {
+    const int r = hw + q * NHW, b = min(max(C.N - 1 - (kb * B + r - lane), 0), C.N - 1);
+    hs[q] = __ldg(C.source + (size_t)zi * C.N + b);
+  }
+}
+template <int B, int NHW>
+__device__ __forceinline__ void cl_help_block(double *ssm, const ClCtx &C, int kb, int hw, int lane, const double (&hs)[(B + NHW - 1) / NHW]) {
+  constexpr int RH = (B + NHW - 1) / NHW, PF = NUSI_CL_PF, D = 2 * B - 1;
+  const int sl = lane, zi = max(C.S - 1 - C.s0 - sl, 0), N = C.N, NT = C.NT;
+  if (hw == 0 && lane < B) {  // where row c of the wave's column sits in the near ring
+    const int w_rel = kb * B + lane, c = NT - 1 - (C.s0 + w_rel), as = max(c - D, 0);
+    reinterpret_cast<int *>(ssm + C.tcoff)[(kb & 1) * B + lane] =
+        C.near + ((kb % NUSI_CL_RB) * B + lane) * NUSI_CL_NEAR + cl_mis(C.tpar, max(c, 0), as) + (c - as);
+  }
+  const double cz = ssm[C.sCz + zi], ndz = ssm[C.sNd + zi];
+  const double U2f[3] = {C.U2f[0], C.U2f[1], C.U2f[2]};
+  double Z[RH][3], rZ[RH][3], Gam[RH], aT[RH], dEb[RH], rdE[RH];
+  bool ok = true;
+#pragma unroll
+  for (int q = 0; q < RH; ++q) {
+    const int r = hw + q * NHW, w_rel = kb * B + r;
+    const int b = min(max(N - 1 - (w_rel - sl), 0), N - 1), c = min(max(NT - 1 - (C.s0 + w_rel), 0), NT - 1);
+    dEb[q] = ssm[C.sdE + b];
+    rdE[q] = ssm[C.sRdE + b];
+    Gam[q] = ndz * __ldg(C.rowG + c);
+    aT[q] = ndz * __ldg(C.rowA + c);
+#pragma unroll
+    for (int kk = 0; kk < 3; ++kk) {
+      const double x = cz * (Gam[q] * U2f[kk] - aT[q] * sqr(U2f[kk]));
+      const double qq = quot_fast(x, dEb[q], rdE[q]);
+      ok = ok && (fabs(qq) <= DBL_MAX);
+      Z[q][kk] = 1.0 + qq;
+    }
+  }
+  if (!ok) {
+#pragma unroll
+    for (int q = 0; q < RH; ++q)
+#pragma unroll
+      for (int kk = 0; kk < 3; ++kk) Z[q][kk] = 1.0 + cz * (Gam[q] * U2f[kk] - aT[q] * sqr(U2f[kk])) / dEb[q];
+  }
+  ok = true;
+#pragma unroll
+  for (int q = 0; q < RH; ++q)
+#pragma unroll
+    for (int kk = 0; kk < 3; ++kk) {
+      rZ[q][kk] = recip_newton(Z[q][kk]);
+      ok = ok && (fabs(Z[q][kk]) < 1e30) && (fabs(Z[q][kk]) > 1e-30);
+    }
+  if (!ok) {
+#pragma unroll
+    for (int q = 0; q < RH; ++q)
+#pragma unroll
+      for (int kk = 0; kk < 3; ++kk) rZ[q][kk] = 1.0 / Z[q][kk];
+  }
+#pragma unroll
+  for (int q = 0; q < RH; ++q) {
+    const int r = hw + q * NHW;
+    if (r < B) {
+      const double offdiag = fabs(aT[q]) * rdE[q] * fmax(fabs(rZ[q][0]), fmax(fabs(rZ[q][1]), fabs(rZ[q][2]))) * 1.00001;
+      double *o = ssm + C.pre + (((kb & 1) * B + r) * PF) * 32 + sl;
+      o[0 * 32] = cz * hs[q]; o[1 * 32] = offdiag; o[2 * 32] = Gam[q]; o[3 * 32] = aT[q];
+      o[4 * 32] = Z[q][0]; o[5 * 32] = rZ[q][0]; o[6 * 32] = Z[q][1]; o[7 * 32] = rZ[q][1]; o[8 * 32] = Z[q][2]; o[9 * 32] = rZ[q][2];
+      o[10 * 32] = dEb[q]; o[11 * 32] = rdE[q];
+    }
+  }
+}
+
+// Column of wave w_rel: c = NT-1-(s0+w_rel), rows 0..c-1 at packed offset c(c-1)/2.  One thread per CTA issues the
+// copies of block kb: this CTA's slice of each of the B columns (rows [a0, a0 + DPC) clipped to [0, c)), and on rank 0
+// the D rows below the diagonal as well.
+template <int B>
+__device__ __forceinline__ void cl_issue_block(const ClCtx &C, int kb) {
+  constexpr int D = 2 * B - 1;
+  const int rb = kb % NUSI_CL_RB;
+  const unsigned bar = C.mbar0 + 8u * rb;
+  const int as = max(C.a0, 0);
+  unsigned total = 0;
+#pragma unroll
+  for (int r = 0; r < B; ++r) {
+    const int w_rel = kb * B + r, c = C.NT - 1 - (C.s0 + w_rel);
+    if (w_rel < C.n_waves && c > 0) {
+      const int len = min(C.a0 + C.DPC, c) - as;
+      if (len > 0) total += (unsigned)((cl_mis(C.tpar, c, as) + len + 1) & ~1) * 8u;
+      if (C.rank == 0) {
+        const int an = max(c - D, 0);
+        total += (unsigned)((cl_mis(C.tpar, c, an) + (c - an) + 1) & ~1) * 8u;
+      }
+    }
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier generic-proxy reads of the slots are ordered before the async writes
+  mbar_expect_tx(bar, total);
+#pragma unroll
+  for (int r = 0; r < B; ++r) {
+    const int w_rel = kb * B + r, c = C.NT - 1 - (C.s0 + w_rel);
+    if (w_rel < C.n_waves && c > 0) {
+      const int len = min(C.a0 + C.DPC, c) - as;
+      if (len > 0) {
+        const int mis = cl_mis(C.tpar, c, as);
+        tma_bulk_g2s(C.ring0 + (unsigned)((rb * B + r) * C.SLOT) * 8u, C.T + cl_packed(c, as) - mis, (unsigned)((mis + len + 1) & ~1) * 8u, bar);
+      }
+      if (C.rank == 0) {
+        const int an = max(c - D, 0), mis = cl_mis(C.tpar, c, an);
+        tma_bulk_g2s(C.near0 + (unsigned)((rb * B + r) * NUSI_CL_NEAR) * 8u, C.T + cl_packed(c, an) - mis, (unsigned)((mis + (c - an) + 1) & ~1) * 8u, bar);
+      }
+    }
+  }
+}
+template <int B, int NHW>
+static __device__ __noinline__ void cl_helper(double *ssm) {
+  constexpr int RH = (B + NHW - 1) / NHW;
+  const ClCtx &C = *reinterpret_cast<const ClCtx *>(ssm);
+  const int lane = threadIdx.x & 31, hw = (threadIdx.x >> 5) - 1, n_blocks = C.n_blocks;
+  const bool work = (C.rank == 0);
+  double hs[RH], hsn[RH];
+  if (work) {
+    cl_help_load<B, NHW>(C, 1, hw, lane, hs);
+    cl_help_load<B, NHW>(C, 2, hw, lane, hsn);
+  }
+  for (int kb = 0; kb < n_blocks; ++kb) {
+    if (threadIdx.x == 32 && kb + 3 < n_blocks) cl_issue_block<B>(C, kb + 3);
+    if (work) {
+      if (kb + 1 < n_blocks) cl_help_block<B, NHW>(ssm, C, kb + 1, hw, lane, hs);
+#pragma unroll
+      for (int q = 0; q < RH; ++q) hs[q] = hsn[q];
+      cl_help_load<B, NHW>(C, kb + 3, hw, lane, hsn);  // clamped indices: harmless beyond the last block
+    }
+    __syncwarp();
+    cl_sync();
+  }
+  // nobody else waits for this CTA's copies of the band's last block: they must have landed before the ring is reused
+  if (threadIdx.x == 32 && n_blocks > 0) mbar_wait(C.mbar0 + 8u * ((n_blocks - 1) % NUSI_CL_RB), cl_parity(C.phase0, n_blocks - 1));
+}
+
+// ================= bulk warps (every rank): sources of block kb-1, publish the diagonal of block kb+1 =================
+template <int B, int NHW>
+static __device__ __noinline__ void cl_bulk(double *ssm) {
+  constexpr int D = 2 * B - 1;
+  const ClCtx &C = *reinterpret_cast<const ClCtx *>(ssm);
+  double acc[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) acc[j] = 0.0;
+  const int N = C.N, u = (int)threadIdx.x - (1 + NHW) * 32;
+  const int d = -31 + C.rank * C.DPC + u;  // this thread's diagonal: cells (sl, b = d + sl)
+  const bool owner = (u < C.DPC) && (d <= N - 1);
+  const int n_blocks = C.n_blocks, n_waves = C.n_waves, cnt = C.cnt;
+  const int wd = N - 1 - d;                // the wave in which the diagonal's cells are finalised
+  const int row = C.a0 + u;                // its table row in this band
+  const int as = max(C.a0, 0);
+  const unsigned mbar0 = C.mbar0, phase0 = C.phase0, tpar = C.tpar;
+  const unsigned ash0 = cl_mapa(C.ash_s, 0u);  // rank 0's hand-over slots
+  for (int kb = 0; kb < n_blocks; ++kb) {
+    if (kb >= 1 && owner) {
+      const int kbs = kb - 1;
+      mbar_wait(mbar0 + 8u * (kbs % NUSI_CL_RB), cl_parity(phase0, kbs));
+#pragma unroll
+      for (int r = 0; r < B; ++r) {
+        const int w_rel = kbs * B + r;
+        if (w_rel < n_waves && wd - w_rel > D && row >= 0) {
+          const int c = C.NT - 1 - (C.s0 + w_rel);
+          const double tv = ssm[C.ring + ((kbs % NUSI_CL_RB) * B + r) * C.SLOT + cl_mis(tpar, c, as) + (row - as)];
+          const double *Wp = ssm + C.wsh + ((kbs & 1) * B + r) * 32;
+          const int hi = min(w_rel, cnt - 1);  // z-steps that have started
+          const unsigned wp_s = (unsigned)__cvta_generic_to_shared(Wp);
+          if (hi == 31) {
+#pragma unroll
+            for (int s8 = 0; s8 < 32; s8 += 8) {
+              double2 w2[4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) w2[q] = lds_f64x2(wp_s + (unsigned)(s8 + 2 * q) * 8u);
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                acc[s8 + 2 * q] = fma(tv, w2[q].x, acc[s8 + 2 * q]);
+                acc[s8 + 2 * q + 1] = fma(tv, w2[q].y, acc[s8 + 2 * q + 1]);
+              }
+            }
+          } else {
+#pragma unroll
+            for (int sl = 0; sl < 32; ++sl)
+              if (sl <= hi) acc[sl] = fma(tv, Wp[sl], acc[sl]);
+          }
+        }
+      }
+    }
+    if (owner) {  // hand the sums of the diagonal that is finalised in block kb+1 to the critical warp
+      const int lo_b = (kb + 1) * B, hi_b = (kb + 2) * B;
+      if (wd >= lo_b && wd < hi_b && wd < n_waves) {
+        const unsigned o = ash0 + (unsigned)((((kb + 1) & 1) * B + (wd - lo_b)) * 32) * 8u;
+#pragma unroll
+        for (int sl = 0; sl < 32; sl += 2) cl_st_f64x2(o + (unsigned)sl * 8u, acc[sl], acc[sl + 1]);
+      }
+    }
+    __syncwarp();
+    cl_sync();
+  }
+}
+
+// B waves per block; NBW bulk warps per CTA (N_bins_E + 31 <= 4 x 32 NBW); NHW helper warps
+template <int B, int NBW, int NHW>
+__global__ void __cluster_dims__(NUSI_CL_C, 1, 1) __launch_bounds__((1 + NHW + NBW) * 32, 1)
+integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, const double *__restrict__ rows,
+                         const double *__restrict__ tri, size_t tstride, double *__restrict__ flux_mass,
+                         double *__restrict__ flux_fla, const int *__restrict__ out_index, const int *__restrict__ status_in,
+                         int *__restrict__ status_out) {
+  constexpr int NTHR = (1 + NHW + NBW) * 32;
+  extern __shared__ __align__(16) double ssm[];
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int rank = (int)cl_rank();
+  const int p = blockIdx.x / NUSI_CL_C;
+  const int N = G.N, NT = G.NT, S = G.Nz - 1;
+  const int DPC = (N + 31 + NUSI_CL_C - 1) / NUSI_CL_C;
+  const bool dead = !(params[p].mphi > 0);
+  const ClLayout L = cl_layout(N, S, B, DPC);
+  ClCtx &C = *reinterpret_cast<ClCtx *>(ssm);
+  double *sdE = ssm + L.sdE, *sRdE = ssm + L.sRdE, *sCz = ssm + L.sCz, *sNd = ssm + L.sNd, *fband = ssm + L.fband;
+  const int NP = (N + 1) & ~1;
+  const unsigned mbar0 = (unsigned)__cvta_generic_to_shared(ssm + L.mbar);
+
+  for (int i = NUSI_CL_CTX_DOUBLES + tid; i < L.pre; i += NTHR) ssm[i] = 0.0;  // rings, pad, W and hand-over slots
+  for (int i = tid; i < S; i += NTHR) {
+    sCz[i] = G.cz[i];
+    sNd[i] = G.ndz[i];
+  }
+  for (int i = tid; i < N; i += NTHR) {
+    sdE[i] = G.dE[i];
+    sRdE[i] = 1.0 / G.dE[i];
+    fband[i] = fband[NP + i] = fband[2 * NP + i] = 0.0;
+  }
+  if (tid == 0) {
+#pragma unroll
+    for (int i = 0; i < NUSI_CL_RB; ++i) mbar_init(mbar0 + 8u * i, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    const PointParams P = params[p];
+    C.N = N; C.NT = NT; C.S = S; C.NP = NP; C.SLOT = L.SLOT; C.DPC = DPC; C.rank = rank;
+    C.ring = L.ring; C.near = L.near; C.wsh = L.wsh; C.ash = L.ash; C.pre = L.pre; C.sdE = L.sdE; C.sRdE = L.sRdE;
+    C.sCz = L.sCz; C.sNd = L.sNd; C.fband = L.fband; C.tcoff = L.tcoff; C.fb = L.fb;
+    C.mbar0 = mbar0;
+    C.ring0 = (unsigned)__cvta_generic_to_shared(ssm + L.ring);
+    C.near0 = (unsigned)__cvta_generic_to_shared(ssm + L.near);
+    C.wsh_s = (unsigned)__cvta_generic_to_shared(ssm + L.wsh);
+    C.ash_s = (unsigned)__cvta_generic_to_shared(ssm + L.ash);
+    C.T = tri + (size_t)p * tstride;
+    C.tpar = (unsigned)(((size_t)C.T >> 3) & 1);  // parity (in doubles) of the table's base address
+    C.source = G.source;
+    C.rowG = rows + ((size_t)p * 2 + 0) * NT;
+    C.rowA = rows + ((size_t)p * 2 + 1) * NT;
+    C.U2f[0] = P.U2f[0]; C.U2f[1] = P.U2f[1]; C.U2f[2] = P.U2f[2];
+  }
+  __syncthreads();
+  cl_sync();  // every CTA's shared memory is initialised before anybody writes into it remotely
+
+  unsigned ring_phase = 0;  // bit i = parity of the next completion of ring block i (tracked identically by every thread)
+  for (int s0 = 0; s0 < S && !dead; s0 += 32) {
+    const int cnt = min(32, S - s0);
+    const int n_waves = cnt - 1 + N, n_blocks = (n_waves + B - 1) / B;
+    if (tid == 0) {
+      C.s0 = s0; C.cnt = cnt; C.n_waves = n_waves; C.n_blocks = n_blocks; C.rowoff = S - 1 - s0; C.phase0 = ring_phase;
+      C.a0 = S - 1 - s0 - 31 + rank * DPC;
+    }
+    for (int i = tid; i < 2 * B * 32; i += NTHR) ssm[L.ash + i] = 0.0;
+    __syncthreads();
+    if (tid == 32) {  // TMA producer of this CTA
+      for (int kb = 0; kb < 3 && kb < n_blocks; ++kb) cl_issue_block<B>(C, kb);
+    }
+    if (rank == 0 && warp >= 1 && warp <= NHW) {
+      double hs0[(B + NHW - 1) / NHW];
+      cl_help_load<B, NHW>(C, 0, warp - 1, tid & 31, hs0);
+      cl_help_block<B, NHW>(ssm, C, 0, warp - 1, tid & 31, hs0);
+    }
+    __syncthreads();
+    cl_sync();
+    if (warp == 0) {
+      if (rank == 0) {
+        cl_critical<B>(ssm);
+      } else {
+        for (int kb = 0; kb < n_blocks; ++kb) cl_sync();
+      }
+    } else if (warp <= NHW) {
+      cl_helper<B, NHW>(ssm);
+    } else {
+      cl_bulk<B, NHW>(ssm);
+    }
+#pragma unroll
+    for (int i = 0; i < NUSI_CL_RB; ++i)
+      if (i < n_blocks && (((n_blocks - 1 - i) / NUSI_CL_RB + 1) & 1)) ring_phase ^= 1u << i;
+    __syncthreads();
+    cl_sync();
+  }
+
+  if (rank == 0) {  // bin-width divide and flavour projection (nuSIprop.hpp:329-336) into this point's output slot
+    const int q = out_index ? out_index[p] : p;
+    for (int b = tid; b < N; b += NTHR) {
+      const double f[3] = {fband[b], fband[NP + b], fband[2 * NP + b]};
+      store_bin(G, flux_mass, flux_fla, q, b, f, sdE[b], dead);
+    }
+    if (status_out && tid == 0) status_out[q] = status_in[p];
+  }
+}
+
+bool integrate_cluster_supports(int N, int NT) { return N > 224 && N + 31 <= NUSI_CL_C * 32 * 16 && NT > 0; }
+
+template <int B, int NBW, int NHW>
+static cudaError_t launch_cluster_t(const IntegArgs &A, cudaStream_t s) {
+  const DeviceGrid &G = A.G;
+  const int DPC = (G.N + 31 + NUSI_CL_C - 1) / NUSI_CL_C;
+  const ClLayout L = cl_layout(G.N, G.Nz - 1, B, DPC);
+  const size_t sh = (size_t)L.total * sizeof(double);
+  cudaError_t e = cudaFuncSetAttribute(integrate_cluster_kernel<B, NBW, NHW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
+  if (e != cudaSuccess) return e;
+  integrate_cluster_kernel<B, NBW, NHW><<<A.cnt * NUSI_CL_C, (1 + NHW + NBW) * 32, sh, s>>>(G, A.params, A.rows, A.tri, A.tstride, A.flux_mass, A.flux_fla,
+                                                                                         A.out_index, A.status_in, A.status_out);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_integrate_cluster(const IntegArgs &A, cudaStream_t s) {
+  const int need = A.G.N + 31;  // diagonals of a band
+  if (need <= NUSI_CL_C * 32 * 4) return launch_cluster_t<4, 4, 2>(A, s);
+  if (need <= NUSI_CL_C * 32 * 8) return launch_cluster_t<4, 8, 2>(A, s);
+  if (need <= NUSI_CL_C * 32 * 16) return launch_cluster_t<4, 16, 2>(A, s);
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace nusi

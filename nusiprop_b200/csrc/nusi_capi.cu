@@ -213,7 +213,7 @@ int nusi_ctx_create(nusi_ctx **out, const nusi_opts *o) {
   if (o->source_model < 0 || o->source_model > 1 ||
       (o->source_model == 1 && (!(std::fabs(1 - o->si) > 1e-12) || !std::isfinite(o->si) || !std::isfinite(o->norm))))
     return fail(NUSI_E_INVALID, "bad source options (source_model 0 or 1; si != 1 and finite; norm finite)");
-  if (o->integrator < 0 || o->integrator > 3 || o->group_max < 0 || o->rows_split < 0 || o->elementary_mode < 0)
+  if (o->integrator < 0 || o->integrator > 4 || o->group_max < 0 || o->rows_split < 0 || o->elementary_mode < 0)
     return fail(NUSI_E_INVALID, "bad implementation switches");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || o->device < 0 || o->device >= ndev)
@@ -615,6 +615,8 @@ static int launch_integrate_stage(nusi_ctx *c, const IntegArgs &A, cudaStream_t 
     e = launch_integrate_wave(A, s);
   else if (c->opt.integrator == 0 && integrate_split_supports(c->G.N, c->G.NT))
     e = launch_integrate_split(A, c->opt.fine_variant, s);
+  else if ((c->opt.integrator == 0 || c->opt.integrator == 4) && integrate_cluster_supports(c->G.N, c->G.NT))
+    e = launch_integrate_cluster(A, s);
   else
     e = launch_integrate_diag(A, c->opt.fine_variant, s);
   if (e == cudaErrorInvalidValue) return fail(NUSI_E_INVALID, "binning not supported by the selected integrator");
