@@ -14,6 +14,7 @@
 //                       diagonal's owner + the last D = 2B-1 sources kept in registers), and BROADCASTS the new weighted
 //                       flux W of the wave into the shared memory of all four CTAs (st.shared::cluster).
 //   rank 0, warps 1..2  helpers: slots (denominators, reciprocals, source term) one block of B waves ahead.
+//   all ranks, 1 warp   producer (one lane): the TMA copies of this CTA's table slices, three blocks ahead.
 //   all ranks, 16 warps bulk: thread u of rank r owns diagonal d = -31 + 508 r + u: acc[s] += T[row(d)][c] W_s for every
 //                       source more than D waves behind its cells, one block behind the critical warp; the owner of the
 //                       diagonal that is finalised in block kb+1 writes its 32 sums into rank 0's shared memory (DSMEM).
@@ -58,7 +59,7 @@ __device__ __forceinline__ void cl_sync() {
 }
 
 struct ClCtx {  // at the start of dynamic shared memory of every CTA, filled by its thread 0
-  int N, NT, S, NP, SLOT, DPC, rank;
+  int N, NT, S, NP, SLOT, DPC, rank, dbg;
   int s0, cnt, n_waves, n_blocks, rowoff, a0;  // a0: table row of this CTA's first diagonal in this band (may be negative)
   int ring, near, wsh, ash, pre, sdE, sRdE, sCz, sNd, fband, tcoff, fb;  // offsets in doubles
   unsigned mbar0, ring0, near0, phase0, tpar, wsh_s, ash_s;              // shared::cta byte addresses
@@ -174,14 +175,19 @@ static __device__ __noinline__ void cl_critical(double *ssm) {
 #pragma unroll
   for (int r = 0; r < NUSI_CL_C; ++r) wdst[r] = cl_mapa(C.wsh_s, (unsigned)r) + (unsigned)sl * 8u;
   for (int kb = 0; kb < n_blocks; ++kb) {
-    mbar_wait(mbar0 + 8u * (kb % NUSI_CL_RB), cl_parity(phase0, kb));
+    if (!(C.dbg & 8)) mbar_wait(mbar0 + 8u * (kb % NUSI_CL_RB), cl_parity(phase0, kb));
     const double *slotB = ssm + C.pre + ((kb & 1) * B * PF) * 32 + sl;
     const double *ashB = ssm + C.ash + (kb & 1) * B * 32 + sl;
     const unsigned woffB = (unsigned)((kb & 1) * B * 32) * 8u;
     const int *tco = reinterpret_cast<const int *>(ssm + C.tcoff) + (kb & 1) * B;
     const int k0 = kb * B - sl;
     const bool all = (cnt == 32) && (kb * B - 31 >= 0) && (kb * B + B - 1 <= N - 1);
-    if (all) {
+    if (C.dbg & 2) {  // timing experiment: no chain
+#pragma unroll
+      for (int r = 0; r < B; ++r)
+#pragma unroll
+        for (int q = 0; q < NUSI_CL_C; ++q) cl_st_f64(wdst[q] + woffB + (unsigned)(r * 32) * 8u, 1e-3);
+    } else if (all) {
 #pragma unroll
       for (int r = 0; r < B; ++r)
         cl_wave<D, true>(true, sl, cnt, N - 1 - (k0 + r), NP, U0, U1, U2, czl, ndl, slotB + r * PF * 32, ashB + r * 32, wdst, woffB + (unsigned)(r * 32) * 8u,
@@ -200,17 +206,25 @@ static __device__ __noinline__ void cl_critical(double *ssm) {
 }
 
 // ================= helper warps (rank 0): slots of block kb+1 =================
+// what a helper fetches from global memory for one of its waves, two blocks before it is used: the source term of the
+// lane's cell and the wave's Gamma / alphaTilde (the same for all lanes)
+struct ClHelpIn {
+  double src, G, A;
+};
 template <int B, int NHW>
-__device__ __forceinline__ void cl_help_load(const ClCtx &C, int kb, int hw, int lane, double (&hs)[(B + NHW - 1) / NHW]) {
+__device__ __forceinline__ void cl_help_load(const ClCtx &C, int kb, int hw, int lane, ClHelpIn (&hs)[(B + NHW - 1) / NHW]) {
   const int zi = max(C.S - 1 - C.s0 - lane, 0);
 #pragma unroll
   for (int q = 0; q < (B + NHW - 1) / NHW; ++q) {
-    const int r = hw + q * NHW, b = min(max(C.N - 1 - (kb * B + r - lane), 0), C.N - 1);
-    hs[q] = __ldg(C.source + (size_t)zi * C.N + b);
+    const int r = hw + q * NHW, w_rel = kb * B + r, b = min(max(C.N - 1 - (w_rel - lane), 0), C.N - 1);
+    const int c = min(max(C.NT - 1 - (C.s0 + w_rel), 0), C.NT - 1);
+    hs[q].src = __ldg(C.source + (size_t)zi * C.N + b);
+    hs[q].G = __ldg(C.rowG + c);
+    hs[q].A = __ldg(C.rowA + c);
   }
 }
 template <int B, int NHW>
-__device__ __forceinline__ void cl_help_block(double *ssm, const ClCtx &C, int kb, int hw, int lane, const double (&hs)[(B + NHW - 1) / NHW]) {
+__device__ __forceinline__ void cl_help_block(double *ssm, const ClCtx &C, int kb, int hw, int lane, const ClHelpIn (&hs)[(B + NHW - 1) / NHW]) {
   constexpr int RH = (B + NHW - 1) / NHW, PF = NUSI_CL_PF, D = 2 * B - 1;
   const int sl = lane, zi = max(C.S - 1 - C.s0 - sl, 0), N = C.N, NT = C.NT;
   if (hw == 0 && lane < B) {  // where row c of the wave's column sits in the near ring
@@ -225,11 +239,11 @@ __device__ __forceinline__ void cl_help_block(double *ssm, const ClCtx &C, int k
 #pragma unroll
   for (int q = 0; q < RH; ++q) {
     const int r = hw + q * NHW, w_rel = kb * B + r;
-    const int b = min(max(N - 1 - (w_rel - sl), 0), N - 1), c = min(max(NT - 1 - (C.s0 + w_rel), 0), NT - 1);
+    const int b = min(max(N - 1 - (w_rel - sl), 0), N - 1);
     dEb[q] = ssm[C.sdE + b];
     rdE[q] = ssm[C.sRdE + b];
-    Gam[q] = ndz * __ldg(C.rowG + c);
-    aT[q] = ndz * __ldg(C.rowA + c);
+    Gam[q] = ndz * hs[q].G;
+    aT[q] = ndz * hs[q].A;
 #pragma unroll
     for (int kk = 0; kk < 3; ++kk) {
       const double x = cz * (Gam[q] * U2f[kk] - aT[q] * sqr(U2f[kk]));
@@ -264,66 +278,94 @@ __device__ __forceinline__ void cl_help_block(double *ssm, const ClCtx &C, int k
     if (r < B) {
       const double offdiag = fabs(aT[q]) * rdE[q] * fmax(fabs(rZ[q][0]), fmax(fabs(rZ[q][1]), fabs(rZ[q][2]))) * 1.00001;
       double *o = ssm + C.pre + (((kb & 1) * B + r) * PF) * 32 + sl;
-      o[0 * 32] = cz * hs[q]; o[1 * 32] = offdiag; o[2 * 32] = Gam[q]; o[3 * 32] = aT[q];
+      o[0 * 32] = cz * hs[q].src; o[1 * 32] = offdiag; o[2 * 32] = Gam[q]; o[3 * 32] = aT[q];
       o[4 * 32] = Z[q][0]; o[5 * 32] = rZ[q][0]; o[6 * 32] = Z[q][1]; o[7 * 32] = rZ[q][1]; o[8 * 32] = Z[q][2]; o[9 * 32] = rZ[q][2];
       o[10 * 32] = dEb[q]; o[11 * 32] = rdE[q];
     }
   }
 }
 
-// Column of wave w_rel: c = NT-1-(s0+w_rel), rows 0..c-1 at packed offset c(c-1)/2.  One thread per CTA issues the
-// copies of block kb: this CTA's slice of each of the B columns (rows [a0, a0 + DPC) clipped to [0, c)), and on rank 0
-// the D rows below the diagonal as well.
+// Column of wave w_rel: c = NT-1-(s0+w_rel), rows 0..c-1 at packed offset c(c-1)/2.  One thread per CTA (lane 0 of the
+// producer warp) issues the copies of block kb: this CTA's slice of each of the B columns (rows [a0, a0 + DPC) clipped
+// to [0, c)), and on rank 0 the D rows below the diagonal as well.  Works on a register copy of the band's fields (the
+// asm statements are memory barriers for the compiler: shared-memory fields would be re-read after every one).
+struct ClIssue {
+  int NT, s0, n_waves, a0, DPC, SLOT, rank;
+  unsigned tpar, mbar0, ring0, near0;
+  const double *T;
+};
+__device__ __forceinline__ ClIssue cl_issue_fields(const ClCtx &C) {
+  ClIssue P;
+  P.NT = C.NT; P.s0 = C.s0; P.n_waves = C.n_waves; P.a0 = C.a0; P.DPC = C.DPC; P.SLOT = C.SLOT; P.rank = C.rank;
+  P.tpar = C.tpar; P.mbar0 = C.mbar0; P.ring0 = C.ring0; P.near0 = C.near0; P.T = C.T;
+  return P;
+}
 template <int B>
-__device__ __forceinline__ void cl_issue_block(const ClCtx &C, int kb) {
+__device__ __forceinline__ void cl_issue_block(const ClIssue &P, int kb) {
   constexpr int D = 2 * B - 1;
   const int rb = kb % NUSI_CL_RB;
-  const unsigned bar = C.mbar0 + 8u * rb;
-  const int as = max(C.a0, 0);
-  unsigned total = 0;
+  const unsigned bar = P.mbar0 + 8u * rb;
+  const int as = max(P.a0, 0);
+  unsigned total = 0, bytes[B], nbytes[B];
+  const double *src[B], *nsrc[B];
 #pragma unroll
   for (int r = 0; r < B; ++r) {
-    const int w_rel = kb * B + r, c = C.NT - 1 - (C.s0 + w_rel);
-    if (w_rel < C.n_waves && c > 0) {
-      const int len = min(C.a0 + C.DPC, c) - as;
-      if (len > 0) total += (unsigned)((cl_mis(C.tpar, c, as) + len + 1) & ~1) * 8u;
-      if (C.rank == 0) {
-        const int an = max(c - D, 0);
-        total += (unsigned)((cl_mis(C.tpar, c, an) + (c - an) + 1) & ~1) * 8u;
+    const int w_rel = kb * B + r, c = P.NT - 1 - (P.s0 + w_rel);
+    bytes[r] = nbytes[r] = 0;
+    src[r] = nsrc[r] = P.T;
+    if (w_rel < P.n_waves && c > 0) {
+      const size_t col = (size_t)c * (size_t)(c - 1) / 2;
+      const int len = min(P.a0 + P.DPC, c) - as;
+      if (len > 0) {
+        const int mis = cl_mis(P.tpar, c, as);
+        bytes[r] = (unsigned)((mis + len + 1) & ~1) * 8u;
+        src[r] = P.T + col + as - mis;
       }
+      if (P.rank == 0) {
+        const int an = max(c - D, 0), mis = cl_mis(P.tpar, c, an);
+        nbytes[r] = (unsigned)((mis + (c - an) + 1) & ~1) * 8u;
+        nsrc[r] = P.T + col + an - mis;
+      }
+      total += bytes[r] + nbytes[r];
     }
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier generic-proxy reads of the slots are ordered before the async writes
   mbar_expect_tx(bar, total);
 #pragma unroll
   for (int r = 0; r < B; ++r) {
-    const int w_rel = kb * B + r, c = C.NT - 1 - (C.s0 + w_rel);
-    if (w_rel < C.n_waves && c > 0) {
-      const int len = min(C.a0 + C.DPC, c) - as;
-      if (len > 0) {
-        const int mis = cl_mis(C.tpar, c, as);
-        tma_bulk_g2s(C.ring0 + (unsigned)((rb * B + r) * C.SLOT) * 8u, C.T + cl_packed(c, as) - mis, (unsigned)((mis + len + 1) & ~1) * 8u, bar);
-      }
-      if (C.rank == 0) {
-        const int an = max(c - D, 0), mis = cl_mis(C.tpar, c, an);
-        tma_bulk_g2s(C.near0 + (unsigned)((rb * B + r) * NUSI_CL_NEAR) * 8u, C.T + cl_packed(c, an) - mis, (unsigned)((mis + (c - an) + 1) & ~1) * 8u, bar);
-      }
-    }
+    if (bytes[r]) tma_bulk_g2s(P.ring0 + (unsigned)((rb * B + r) * P.SLOT) * 8u, src[r], bytes[r], bar);
+    if (nbytes[r]) tma_bulk_g2s(P.near0 + (unsigned)((rb * B + r) * NUSI_CL_NEAR) * 8u, nsrc[r], nbytes[r], bar);
   }
 }
+// ================= producer warp (every rank): table copies of block kb+3 =================
+template <int B>
+static __device__ __noinline__ void cl_producer(double *ssm) {
+  const ClCtx &C = *reinterpret_cast<const ClCtx *>(ssm);
+  const int n_blocks = C.n_blocks;
+  const bool on = ((threadIdx.x & 31) == 0) && !(C.dbg & 8);
+  const ClIssue P = cl_issue_fields(C);
+  const unsigned phase0 = C.phase0;
+  for (int kb = 0; kb < n_blocks; ++kb) {
+    if (on && kb + 3 < n_blocks) cl_issue_block<B>(P, kb + 3);
+    __syncwarp();
+    cl_sync();
+  }
+  // nobody else waits for this CTA's copies of the band's last block: they must have landed before the ring is reused
+  if (on && n_blocks > 0) mbar_wait(P.mbar0 + 8u * ((n_blocks - 1) % NUSI_CL_RB), cl_parity(phase0, n_blocks - 1));
+}
+
 template <int B, int NHW>
 static __device__ __noinline__ void cl_helper(double *ssm) {
   constexpr int RH = (B + NHW - 1) / NHW;
   const ClCtx &C = *reinterpret_cast<const ClCtx *>(ssm);
   const int lane = threadIdx.x & 31, hw = (threadIdx.x >> 5) - 1, n_blocks = C.n_blocks;
-  const bool work = (C.rank == 0);
-  double hs[RH], hsn[RH];
+  const bool work = (C.rank == 0) && !(C.dbg & 4);
+  ClHelpIn hs[RH], hsn[RH];
   if (work) {
     cl_help_load<B, NHW>(C, 1, hw, lane, hs);
     cl_help_load<B, NHW>(C, 2, hw, lane, hsn);
   }
   for (int kb = 0; kb < n_blocks; ++kb) {
-    if (threadIdx.x == 32 && kb + 3 < n_blocks) cl_issue_block<B>(C, kb + 3);
     if (work) {
       if (kb + 1 < n_blocks) cl_help_block<B, NHW>(ssm, C, kb + 1, hw, lane, hs);
 #pragma unroll
@@ -333,8 +375,6 @@ static __device__ __noinline__ void cl_helper(double *ssm) {
     __syncwarp();
     cl_sync();
   }
-  // nobody else waits for this CTA's copies of the band's last block: they must have landed before the ring is reused
-  if (threadIdx.x == 32 && n_blocks > 0) mbar_wait(C.mbar0 + 8u * ((n_blocks - 1) % NUSI_CL_RB), cl_parity(C.phase0, n_blocks - 1));
 }
 
 // ================= bulk warps (every rank): sources of block kb-1, publish the diagonal of block kb+1 =================
@@ -345,7 +385,7 @@ static __device__ __noinline__ void cl_bulk(double *ssm) {
   double acc[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) acc[j] = 0.0;
-  const int N = C.N, u = (int)threadIdx.x - (1 + NHW) * 32;
+  const int N = C.N, u = (int)threadIdx.x - (2 + NHW) * 32;
   const int d = -31 + C.rank * C.DPC + u;  // this thread's diagonal: cells (sl, b = d + sl)
   const bool owner = (u < C.DPC) && (d <= N - 1);
   const int n_blocks = C.n_blocks, n_waves = C.n_waves, cnt = C.cnt;
@@ -355,7 +395,7 @@ static __device__ __noinline__ void cl_bulk(double *ssm) {
   const unsigned mbar0 = C.mbar0, phase0 = C.phase0, tpar = C.tpar;
   const unsigned ash0 = cl_mapa(C.ash_s, 0u);  // rank 0's hand-over slots
   for (int kb = 0; kb < n_blocks; ++kb) {
-    if (kb >= 1 && owner) {
+    if (kb >= 1 && owner && !(C.dbg & 1)) {
       const int kbs = kb - 1;
       mbar_wait(mbar0 + 8u * (kbs % NUSI_CL_RB), cl_parity(phase0, kbs));
 #pragma unroll
@@ -402,12 +442,12 @@ static __device__ __noinline__ void cl_bulk(double *ssm) {
 
 // B waves per block; NBW bulk warps per CTA (N_bins_E + 31 <= 4 x 32 NBW); NHW helper warps
 template <int B, int NBW, int NHW>
-__global__ void __cluster_dims__(NUSI_CL_C, 1, 1) __launch_bounds__((1 + NHW + NBW) * 32, 1)
+__global__ void __cluster_dims__(NUSI_CL_C, 1, 1) __launch_bounds__((2 + NHW + NBW) * 32, (NBW <= 4 ? 2 : 1))
 integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, const double *__restrict__ rows,
                          const double *__restrict__ tri, size_t tstride, double *__restrict__ flux_mass,
                          double *__restrict__ flux_fla, const int *__restrict__ out_index, const int *__restrict__ status_in,
-                         int *__restrict__ status_out) {
-  constexpr int NTHR = (1 + NHW + NBW) * 32;
+                         int *__restrict__ status_out, int dbg) {
+  constexpr int NTHR = (2 + NHW + NBW) * 32;  // critical | helpers | producer | bulk
   extern __shared__ __align__(16) double ssm[];
   const int tid = threadIdx.x, warp = tid >> 5;
   const int rank = (int)cl_rank();
@@ -436,7 +476,7 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
     for (int i = 0; i < NUSI_CL_RB; ++i) mbar_init(mbar0 + 8u * i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     const PointParams P = params[p];
-    C.N = N; C.NT = NT; C.S = S; C.NP = NP; C.SLOT = L.SLOT; C.DPC = DPC; C.rank = rank;
+    C.N = N; C.NT = NT; C.S = S; C.NP = NP; C.SLOT = L.SLOT; C.DPC = DPC; C.rank = rank; C.dbg = dbg;
     C.ring = L.ring; C.near = L.near; C.wsh = L.wsh; C.ash = L.ash; C.pre = L.pre; C.sdE = L.sdE; C.sRdE = L.sRdE;
     C.sCz = L.sCz; C.sNd = L.sNd; C.fband = L.fband; C.tcoff = L.tcoff; C.fb = L.fb;
     C.mbar0 = mbar0;
@@ -464,11 +504,12 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
     }
     for (int i = tid; i < 2 * B * 32; i += NTHR) ssm[L.ash + i] = 0.0;
     __syncthreads();
-    if (tid == 32) {  // TMA producer of this CTA
-      for (int kb = 0; kb < 3 && kb < n_blocks; ++kb) cl_issue_block<B>(C, kb);
+    if (tid == (1 + NHW) * 32) {  // TMA producer of this CTA
+      const ClIssue P = cl_issue_fields(C);
+      for (int kb = 0; kb < 3 && kb < n_blocks && !(dbg & 8); ++kb) cl_issue_block<B>(P, kb);
     }
     if (rank == 0 && warp >= 1 && warp <= NHW) {
-      double hs0[(B + NHW - 1) / NHW];
+      ClHelpIn hs0[(B + NHW - 1) / NHW];
       cl_help_load<B, NHW>(C, 0, warp - 1, tid & 31, hs0);
       cl_help_block<B, NHW>(ssm, C, 0, warp - 1, tid & 31, hs0);
     }
@@ -482,6 +523,8 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
       }
     } else if (warp <= NHW) {
       cl_helper<B, NHW>(ssm);
+    } else if (warp == 1 + NHW) {
+      cl_producer<B>(ssm);
     } else {
       cl_bulk<B, NHW>(ssm);
     }
@@ -505,23 +548,25 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
 bool integrate_cluster_supports(int N, int NT) { return N > 224 && N + 31 <= NUSI_CL_C * 32 * 16 && NT > 0; }
 
 template <int B, int NBW, int NHW>
-static cudaError_t launch_cluster_t(const IntegArgs &A, cudaStream_t s) {
+static cudaError_t launch_cluster_t(const IntegArgs &A, cudaStream_t s, int dbg) {
   const DeviceGrid &G = A.G;
   const int DPC = (G.N + 31 + NUSI_CL_C - 1) / NUSI_CL_C;
   const ClLayout L = cl_layout(G.N, G.Nz - 1, B, DPC);
   const size_t sh = (size_t)L.total * sizeof(double);
   cudaError_t e = cudaFuncSetAttribute(integrate_cluster_kernel<B, NBW, NHW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
   if (e != cudaSuccess) return e;
-  integrate_cluster_kernel<B, NBW, NHW><<<A.cnt * NUSI_CL_C, (1 + NHW + NBW) * 32, sh, s>>>(G, A.params, A.rows, A.tri, A.tstride, A.flux_mass, A.flux_fla,
-                                                                                         A.out_index, A.status_in, A.status_out);
+  integrate_cluster_kernel<B, NBW, NHW><<<A.cnt * NUSI_CL_C, (2 + NHW + NBW) * 32, sh, s>>>(G, A.params, A.rows, A.tri, A.tstride, A.flux_mass, A.flux_fla,
+                                                                                         A.out_index, A.status_in, A.status_out, dbg);
   return cudaGetLastError();
 }
 
-cudaError_t launch_integrate_cluster(const IntegArgs &A, cudaStream_t s) {
+// variant: 0 = the product configuration; 20 + bits = timing experiments with wrong results (1 no bulk update, 2 no critical chain, 4 no helper work, 8 no table copies)
+cudaError_t launch_integrate_cluster(const IntegArgs &A, int variant, cudaStream_t s) {
   const int need = A.G.N + 31;  // diagonals of a band
-  if (need <= NUSI_CL_C * 32 * 4) return launch_cluster_t<4, 4, 2>(A, s);
-  if (need <= NUSI_CL_C * 32 * 8) return launch_cluster_t<4, 8, 2>(A, s);
-  if (need <= NUSI_CL_C * 32 * 16) return launch_cluster_t<4, 16, 2>(A, s);
+  const int dbg = variant >= 20 ? variant - 20 : 0;
+  if (need <= NUSI_CL_C * 32 * 4) return launch_cluster_t<4, 4, 2>(A, s, dbg);
+  if (need <= NUSI_CL_C * 32 * 8) return launch_cluster_t<4, 8, 2>(A, s, dbg);
+  if (need <= NUSI_CL_C * 32 * 16) return launch_cluster_t<4, 16, 2>(A, s, dbg);
   return cudaErrorInvalidValue;
 }
 

@@ -66,7 +66,7 @@ cudaError_t launch_integrate_split(const IntegArgs &A, int variant, cudaStream_t
 bool integrate_split_supports(int N, int NT);
 // k_integrate_cluster.cu -- product kernel for fine binnings (224 < N_bins_E <= 2017): the role-split wavefront with one point
 // spread over a thread-block cluster of 4 CTAs
-cudaError_t launch_integrate_cluster(const IntegArgs &A, cudaStream_t s);
+cudaError_t launch_integrate_cluster(const IntegArgs &A, int variant, cudaStream_t s);
 bool integrate_cluster_supports(int N, int NT);
 // k_integrate_check.cu -- bin-owned wavefront, serial reference-shaped, resonant-only
 cudaError_t launch_integrate_wave(const IntegArgs &A, cudaStream_t s);
