@@ -14,7 +14,7 @@
 //                       diagonal's owner + the last D = 2B-1 sources kept in registers), and BROADCASTS the new weighted
 //                       flux W of the wave into the shared memory of all four CTAs (st.shared::cluster).
 //   rank 0, warps 1..2  helpers: slots (denominators, reciprocals, source term) one block of B waves ahead.
-//   all ranks, 1 warp   producer (one lane): the TMA copies of this CTA's table slices, three blocks ahead.
+//   all ranks, 1 warp   producer (one lane per copy): the TMA copies of this CTA's table slices, three blocks ahead.
 //   all ranks, 16 warps bulk: thread u of rank r owns diagonal d = -31 + 508 r + u: acc[s] += T[row(d)][c] W_s for every
 //                       source more than D waves behind its cells, one block behind the critical warp; the owner of the
 //                       diagonal that is finalised in block kb+1 writes its 32 sums into rank 0's shared memory (DSMEM).
@@ -300,58 +300,56 @@ __device__ __forceinline__ ClIssue cl_issue_fields(const ClCtx &C) {
   P.tpar = C.tpar; P.mbar0 = C.mbar0; P.ring0 = C.ring0; P.near0 = C.near0; P.T = C.T;
   return P;
 }
+// Called by the WHOLE producer warp: lane r (< B) copies this CTA's slice of column r of the block, lane B + r (rank 0 only)
+// the D rows below the diagonal of that column; lane 0 announces the byte count first.
 template <int B>
-__device__ __forceinline__ void cl_issue_block(const ClIssue &P, int kb) {
+__device__ __forceinline__ void cl_issue_block(const ClIssue &P, int kb, int lane) {
   constexpr int D = 2 * B - 1;
   const int rb = kb % NUSI_CL_RB;
   const unsigned bar = P.mbar0 + 8u * rb;
   const int as = max(P.a0, 0);
-  unsigned total = 0, bytes[B], nbytes[B];
-  const double *src[B], *nsrc[B];
-#pragma unroll
-  for (int r = 0; r < B; ++r) {
-    const int w_rel = kb * B + r, c = P.NT - 1 - (P.s0 + w_rel);
-    bytes[r] = nbytes[r] = 0;
-    src[r] = nsrc[r] = P.T;
-    if (w_rel < P.n_waves && c > 0) {
-      const size_t col = (size_t)c * (size_t)(c - 1) / 2;
+  const int r = lane & (B - 1), kind = lane / B;  // B is a power of two
+  const int w_rel = kb * B + r, c = P.NT - 1 - (P.s0 + w_rel);
+  unsigned bytes = 0, dst = 0;
+  const double *src = P.T;
+  if (kind <= 1 && w_rel < P.n_waves && c > 0) {
+    const size_t col = (size_t)c * (size_t)(c - 1) / 2;
+    if (kind == 0) {
       const int len = min(P.a0 + P.DPC, c) - as;
       if (len > 0) {
         const int mis = cl_mis(P.tpar, c, as);
-        bytes[r] = (unsigned)((mis + len + 1) & ~1) * 8u;
-        src[r] = P.T + col + as - mis;
+        bytes = (unsigned)((mis + len + 1) & ~1) * 8u;
+        src = P.T + col + as - mis;
+        dst = P.ring0 + (unsigned)((rb * B + r) * P.SLOT) * 8u;
       }
-      if (P.rank == 0) {
-        const int an = max(c - D, 0), mis = cl_mis(P.tpar, c, an);
-        nbytes[r] = (unsigned)((mis + (c - an) + 1) & ~1) * 8u;
-        nsrc[r] = P.T + col + an - mis;
-      }
-      total += bytes[r] + nbytes[r];
+    } else if (P.rank == 0) {
+      const int an = max(c - D, 0), mis = cl_mis(P.tpar, c, an);
+      bytes = (unsigned)((mis + (c - an) + 1) & ~1) * 8u;
+      src = P.T + col + an - mis;
+      dst = P.near0 + (unsigned)((rb * B + r) * NUSI_CL_NEAR) * 8u;
     }
   }
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier generic-proxy reads of the slots are ordered before the async writes
-  mbar_expect_tx(bar, total);
-#pragma unroll
-  for (int r = 0; r < B; ++r) {
-    if (bytes[r]) tma_bulk_g2s(P.ring0 + (unsigned)((rb * B + r) * P.SLOT) * 8u, src[r], bytes[r], bar);
-    if (nbytes[r]) tma_bulk_g2s(P.near0 + (unsigned)((rb * B + r) * NUSI_CL_NEAR) * 8u, nsrc[r], nbytes[r], bar);
-  }
+  const unsigned total = __reduce_add_sync(0xffffffffu, bytes);
+  if (lane == 0) mbar_expect_tx(bar, total);
+  __syncwarp();
+  if (bytes) tma_bulk_g2s(dst, src, bytes, bar);
 }
 // ================= producer warp (every rank): table copies of block kb+3 =================
 template <int B>
 static __device__ __noinline__ void cl_producer(double *ssm) {
   const ClCtx &C = *reinterpret_cast<const ClCtx *>(ssm);
   const int n_blocks = C.n_blocks;
-  const bool on = ((threadIdx.x & 31) == 0) && !(C.dbg & 8);
+  const int lane = threadIdx.x & 31;
+  const bool on = !(C.dbg & 8);
   const ClIssue P = cl_issue_fields(C);
   const unsigned phase0 = C.phase0;
   for (int kb = 0; kb < n_blocks; ++kb) {
-    if (on && kb + 3 < n_blocks) cl_issue_block<B>(P, kb + 3);
+    if (on && kb + 3 < n_blocks) cl_issue_block<B>(P, kb + 3, lane);
     __syncwarp();
     cl_sync();
   }
   // nobody else waits for this CTA's copies of the band's last block: they must have landed before the ring is reused
-  if (on && n_blocks > 0) mbar_wait(P.mbar0 + 8u * ((n_blocks - 1) % NUSI_CL_RB), cl_parity(phase0, n_blocks - 1));
+  if (on && lane == 0 && n_blocks > 0) mbar_wait(P.mbar0 + 8u * ((n_blocks - 1) % NUSI_CL_RB), cl_parity(phase0, n_blocks - 1));
 }
 
 template <int B, int NHW>
@@ -491,6 +489,7 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
     C.rowA = rows + ((size_t)p * 2 + 1) * NT;
     C.U2f[0] = P.U2f[0]; C.U2f[1] = P.U2f[1]; C.U2f[2] = P.U2f[2];
   }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the zeroed rings are written by the async proxy from here on
   __syncthreads();
   cl_sync();  // every CTA's shared memory is initialised before anybody writes into it remotely
 
@@ -504,9 +503,9 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
     }
     for (int i = tid; i < 2 * B * 32; i += NTHR) ssm[L.ash + i] = 0.0;
     __syncthreads();
-    if (tid == (1 + NHW) * 32) {  // TMA producer of this CTA
+    if (warp == 1 + NHW) {  // TMA producer warp of this CTA
       const ClIssue P = cl_issue_fields(C);
-      for (int kb = 0; kb < 3 && kb < n_blocks && !(dbg & 8); ++kb) cl_issue_block<B>(P, kb);
+      for (int kb = 0; kb < 3 && kb < n_blocks && !(dbg & 8); ++kb) cl_issue_block<B>(P, kb, tid & 31);
     }
     if (rank == 0 && warp >= 1 && warp <= NHW) {
       ClHelpIn hs0[(B + NHW - 1) / NHW];
