@@ -109,6 +109,19 @@ def load():
     return lib
 
 
+def load_path(path):
+    """An ALTERNATIVE build of the same library (tests: the libm-locked build), not cached; pass it to
+    Context(_library=...).  The product always uses load()."""
+    if not os.path.exists(path):
+        raise NusiError("library %s not found" % path)
+    lib = C.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
 def check(rc, what=""):
     if rc != 0:
         lib = load()

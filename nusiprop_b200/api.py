@@ -31,10 +31,10 @@ class Context(object):
 
     def __init__(self, majorana=True, non_resonant=True, normal_ordering=True, N_bins_E=300, lEmin=12.0,
                  lEmax=17.0, zmax=5.0, flav=2, phiphi=False, device=0, alphatilde_phiphi_path=None,
-                 alpha_phiphi_path=None, max_points_per_launch=0, elementary_mode=None, source_model=0, si=2.0, norm=1.0, **switches):
+                 alpha_phiphi_path=None, max_points_per_launch=0, elementary_mode=None, source_model=0, si=2.0, norm=1.0, _library=None, **switches):
         """switches: the implementation switches of nusi_opts (integrator, fine_variant, builder_per_entry, group_max,
         group_always, rows_split, rows_ungrouped, keep_order, two_stream, source_device); all default 0."""
-        self._lib = _lib.load()
+        self._lib = _library or _lib.load()  # _library: an alternative build of the library (tests only)
         o = NusiOpts()
         check(self._lib.nusi_opts_default(C.byref(o)), "nusi_opts_default")
         o.majorana, o.non_resonant, o.normal_ordering = int(bool(majorana)), int(bool(non_resonant)), int(bool(normal_ordering))

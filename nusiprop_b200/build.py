@@ -35,7 +35,7 @@ def _deps(path, seen=None):
 
 def build_library(force=False, verbose=False, extra_flags=(), out=None):
     """Compile every translation unit whose object is older than its source or any header, then link.
-    extra_flags / out: alternative builds of the same sources (tests: -DNUSI_LOCKED_LIBM; tuning experiments)."""
+    extra_flags / out: alternative builds of the same sources (tests: -DNUSI_LOCKED_MATH; tuning experiments)."""
     out = out or OUT
     obj_dir = OBJ_DIR if out == OUT else os.path.join(os.path.dirname(out), "build_" + os.path.basename(out))
     os.makedirs(obj_dir, exist_ok=True)
@@ -64,6 +64,15 @@ def build_library(force=False, verbose=False, extra_flags=(), out=None):
     if jobs or not os.path.exists(out):
         subprocess.check_call([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", out] + objs)
     return out
+
+
+LOCKED_OUT = os.path.join(_HERE, "lib", "libnusiprop_b200_locked.so")
+
+
+def build_locked_library(force=False):
+    """TEST build of the same sources with -DNUSI_LOCKED_MATH: every elementary function from csrc/nusi_locked_math.h, the
+    counterpart of oracle/_ref/libnusi_ref_locked.so (tests/test_locked_parity.py).  Never loaded by the package."""
+    return build_library(force=force, extra_flags=["-DNUSI_LOCKED_MATH"], out=LOCKED_OUT)
 
 
 ROOT = os.path.dirname(_HERE)

@@ -133,7 +133,7 @@ NUSI_HD int alphatilde_mass(const PointParams &P, const PhiPhiTables *pp, int k,
     const double combi = atilde_dilog_combi(tminus, tplus);
     Atu = g4 / (32 * kPi * m4 * (1 + tminus) * tplus) *
           (2 * (2 * (1 + tminus) * (tminus - tplus) -
-                2 * (1 + tminus) * tplus * atanh(1 / (1 - tplus)) * atanh((tminus - tplus) / (-2 + tminus + tplus)) +
+                2 * (1 + tminus) * tplus * natanh(1 / (1 - tplus)) * natanh((tminus - tplus) / (-2 + tminus + tplus)) +
                 tminus * tplus * (-lm + lp) + (1 + tminus) * (lm - lp - ld) + tplus * (-lm + lp + ld) -
                 tminus * tplus * lrat) +
            (1 + tminus) * tplus * ((-sqr(lm) + sqr(lp)) / 2. + dilog1over1mdiff(tplus, tminus)) -
@@ -270,7 +270,7 @@ NUSI_HD void alphatilde_mass_shared(double mphi, double mnk, double Em, double E
   const double combi = atilde_dilog_combi(tminus, tplus);
   S.den_tu = (32 * kPi * m4 * (1 + tminus) * tplus);
   S.Btu = (2 * (2 * (1 + tminus) * (tminus - tplus) -
-                2 * (1 + tminus) * tplus * atanh(1 / (1 - tplus)) * atanh((tminus - tplus) / (-2 + tminus + tplus)) +
+                2 * (1 + tminus) * tplus * natanh(1 / (1 - tplus)) * natanh((tminus - tplus) / (-2 + tminus + tplus)) +
                 tminus * tplus * (-lm + lp) + (1 + tminus) * (lm - lp - ld) + tplus * (-lm + lp + ld) -
                 tminus * tplus * lrat) +
            (1 + tminus) * tplus * ((-sqr(lm) + sqr(lp)) / 2. + dilog1over1mdiff(tplus, tminus)) -

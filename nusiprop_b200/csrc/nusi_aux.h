@@ -29,7 +29,7 @@ struct PointParams {
 
 // atan(x) - atan(y), series when both are large and of the same sign (aux.hpp:63-75)
 NUSI_HD double atandiff(double x, double y) {
-  if (fabs(x) < 1e2 || fabs(y) < 1e2 || x * y < 0) return atan(x) - atan(y);
+  if (fabs(x) < 1e2 || fabs(y) < 1e2 || x * y < 0) return natan(x) - natan(y);
   return -1. / x + cub(1. / x) / 3. - (-1. / y + cub(1. / y) / 3.);
 }
 

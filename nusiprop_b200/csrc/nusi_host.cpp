@@ -1,5 +1,13 @@
 // nusi_host.cpp -- see nusi_host.hpp.  Compiled with -ffp-contract=off so every expression
 // rounds exactly as written (the oracle build uses the same flag).
+// The one elementary function the host side shares with the reference's constructor / source / table-loader code is log():
+// the libm-locked test build (NUSI_LOCKED_MATH) routes it to the same source as the locked oracle.
+#ifdef NUSI_LOCKED_MATH
+#include "nusi_locked_math.h"
+#define NUSI_HOST_LOG(x) nusi_locked::log(x)
+#else
+#define NUSI_HOST_LOG(x) std::log(x)
+#endif
 #include "nusi_host.hpp"
 #include "nusi_interp.h"
 #include <cmath>
@@ -33,7 +41,7 @@ void build_grid(int N, double lEmin, double lEmax, double zmax, bool normal_orde
     G.dE[i] = G.Emax[i] - G.Emin[i];
   }
   // redshift step = energy step (nuSIprop.hpp:120-128); the (int) truncation is the reference's
-  G.Nz = (int)(std::log((1 + zmax) / (1 + 0)) / std::log(G.Emax[0] / G.Emin[0]) + 2);
+  G.Nz = (int)(NUSI_HOST_LOG((1 + zmax) / (1 + 0)) / NUSI_HOST_LOG(G.Emax[0] / G.Emin[0]) + 2);
   G.z.resize(G.Nz);
   for (int i = 0; i < G.Nz; ++i) G.z[i] = (1 + 0) * std::pow(G.Emax[0] / G.Emin[0], i) - 1;
   G.zmax_eff = G.z[G.Nz - 1];
@@ -51,7 +59,7 @@ void build_grid(int N, double lEmin, double lEmax, double zmax, bool normal_orde
     }
   }
 
-  const double dlogz = std::log(1 + G.z[1]) - std::log(1 + G.z[0]);
+  const double dlogz = NUSI_HOST_LOG(1 + G.z[1]) - NUSI_HOST_LOG(1 + G.z[0]);
   const int S = G.Nz - 1;
   G.cz.resize(S);
   G.ndz.resize(S);
@@ -141,7 +149,7 @@ double freestream_energy(double zmax_eff, double lEmin, double lEmax, double si,
     const double Em = std::pow(10, lEmin), Ep = std::pow(10, lEmax);
     if (std::fabs(si - 2) < 1e-5)
       return norm_total * cosmo_SFR(z) * std::pow(E0 / (1 + z), si) *
-             (std::log(Ep / Em) + (2 - si) / 2.0 * (sqr(std::log(Ep)) - sqr(std::log(Em))));
+             (NUSI_HOST_LOG(Ep / Em) + (2 - si) / 2.0 * (sqr(NUSI_HOST_LOG(Ep)) - sqr(NUSI_HOST_LOG(Em))));
     return norm_total * cosmo_SFR(z) * std::pow(E0 / (1 + z), si) * (std::pow(Ep, 2 - si) - std::pow(Em, 2 - si)) / (2 - si);
   };
   return gl3_panels(0, zmax_eff, [&](double z) { return lum_times_E(z) / cosmo_H(z); });
@@ -150,7 +158,7 @@ double freestream_energy(double zmax_eff, double lEmin, double lEmax, double si,
 // nuSIprop.hpp:638-646, expression for expression (log(exp(-x) + 1), not log1p; pow-free prefactor handed in)
 static double dsnb_lum_int(double pref, double z, double E) {
   const double Tnue = 6e6;
-  return pref * (-E * E * (1 + z) * std::log(std::exp(-E * (1 + z) / Tnue) + 1) / Tnue + 2 * E * li2_neg(-std::exp(-E * (1 + z) / Tnue)) +
+  return pref * (-E * E * (1 + z) * NUSI_HOST_LOG(std::exp(-E * (1 + z) / Tnue) + 1) / Tnue + 2 * E * li2_neg(-std::exp(-E * (1 + z) / Tnue)) +
                  2 * Tnue * li3_neg(-std::exp(-E * (1 + z) / Tnue)) / (1 + z));
 }
 void dsnb_source(int N, int S, const double *zsrc, const double *rsn, double pref, const double *Emin, const double *Emax, double *out) {
@@ -167,7 +175,7 @@ void dsnb_source(int N, int S, const double *zsrc, const double *rsn, double pre
 double freestream_energy_dsnb(double zmax_eff, double lEmin, double lEmax) {
   const double Etot = 3 * 6.24, Tnue = 6e6;
   auto dNdE = [&](double E) { return Etot * 120 * std::pow(E, 2) / (6 * 7 * std::pow(M_PI, 4) * std::pow(Tnue, 4) * (std::exp(E / Tnue) + 1)); };
-  const double la = lEmin * std::log(10.0), lb = lEmax * std::log(10.0);
+  const double la = lEmin * NUSI_HOST_LOG(10.0), lb = lEmax * NUSI_HOST_LOG(10.0);
   auto e_integral = [&](double z) {
     const int n_panels = 400;
     double res = 0;
@@ -328,7 +336,7 @@ std::string load_phiphi(const char *at_path, const char *a_path, double l10d, Ho
     T.delta_in_range = interp_inside(x1.data(), n1, l10d) ? 1 : 0;
     T.at_x0.resize(n0);
     T.at_f.assign(n0, 0.0);
-    for (int a = 0; a < n0; ++a) T.at_x0[a] = std::log((double)buf[((size_t)a * n1) * 3 + 0]);
+    for (int a = 0; a < n0; ++a) T.at_x0[a] = NUSI_HOST_LOG((double)buf[((size_t)a * n1) * 3 + 0]);
     if (T.delta_in_range) {
       AxisStencil S;
       interp_axis(x1.data(), n1, l10d, S);
@@ -353,7 +361,7 @@ std::string load_phiphi(const char *at_path, const char *a_path, double l10d, Ho
     T.a_x0.resize(n0);
     T.a_x1.resize(n1);
     T.a_f.assign((size_t)n0 * n1, 0.0);
-    for (int a = 0; a < n0; ++a) T.a_x0[a] = std::log((double)buf[((size_t)a * n1 * n2) * 4 + 0]);
+    for (int a = 0; a < n0; ++a) T.a_x0[a] = NUSI_HOST_LOG((double)buf[((size_t)a * n1 * n2) * 4 + 0]);
     for (int b = 0; b < n1; ++b) T.a_x1[b] = (double)buf[((size_t)b * n2) * 4 + 1];
     if (in2) {
       AxisStencil S;

@@ -114,7 +114,7 @@ NUSI_HD bool interp_inside(const double *x, int n, double x0) { return (x0 > x[0
 
 // alphaTilde_phiphi at (|tbar_plus|, log10 delta)   <- spl_alphaTilde_phiphi.f_eval  nuSIprop.hpp:1199
 NUSI_HD double phiphi_alphatilde_eval(const PhiPhiTables *T, double abs_tplus, double /*log10_delta*/, int *warn) {
-  const double x0 = log(abs_tplus);
+  const double x0 = nlog(abs_tplus);
   if (!T || !T->at_f || !T->delta_in_range || !interp_inside(T->at_x0, T->at_n0, x0)) {
     if (warn) *warn |= NUSI_WARN_PP_RANGE;
     return NAN;
@@ -128,7 +128,7 @@ NUSI_HD double phiphi_alphatilde_eval(const PhiPhiTables *T, double abs_tplus, d
 
 // alpha_phiphi at (sbar, n, log10 delta)            <- spl_alpha_phiphi.f_eval       nuSIprop.hpp:1483
 NUSI_HD double phiphi_alpha_eval(const PhiPhiTables *T, double sbar, double n, double /*log10_delta*/, int *warn) {
-  const double x0 = log(sbar);
+  const double x0 = nlog(sbar);
   if (!T || !T->a_f || !T->delta_in_range || !interp_inside(T->a_x0, T->a_n0, x0) ||
       !interp_inside(T->a_x1, T->a_n1, n)) {
     if (warn) *warn |= NUSI_WARN_PP_RANGE;

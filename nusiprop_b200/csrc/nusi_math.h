@@ -38,6 +38,19 @@ namespace nusi {
 // Elementary functions.  On the device each is ONE out-of-line copy (CUDA inlines ~1-3 KB of SASS
 // per call site otherwise, and the builder kernels have ~60 call sites: the instruction cache is
 // the first bottleneck of this path).  On the host they are the libm calls.
+#if defined(NUSI_LOCKED_MATH)
+// libm-locked build (tests only): every elementary function is nusi_locked_math.h -- the same source and
+// the same bits on the host and on the device, shared with oracle/_ref/libnusi_ref_locked.so.
+}  // namespace nusi
+#include "nusi_locked_math.h"
+namespace nusi {
+NUSI_HD_NOINLINE double nlog(double x) { return nusi_locked::log(x); }
+NUSI_HD_NOINLINE double nlog1p(double x) { return nusi_locked::log1p(x); }
+NUSI_HD_NOINLINE double natan2(double y, double x) { return nusi_locked::atan2(y, x); }
+NUSI_HD_NOINLINE double natan(double x) { return nusi_locked::atan(x); }
+NUSI_HD_NOINLINE double natanh(double x) { return nusi_locked::atanh(x); }
+NUSI_HD double nhypot(double x, double y) { return nusi_locked::hypot(x, y); }
+#else
 #if defined(__CUDA_ARCH__)
 static __device__ __noinline__ double nlog(double x) { return ::log(x); }
 static __device__ __noinline__ double nlog1p(double x) { return ::log1p(x); }
@@ -46,6 +59,10 @@ static __device__ __noinline__ double natan2(double y, double x) { return ::atan
 inline double nlog(double x) { return ::log(x); }
 inline double nlog1p(double x) { return ::log1p(x); }
 inline double natan2(double y, double x) { return ::atan2(y, x); }
+#endif
+NUSI_HD double natan(double x) { return ::atan(x); }
+NUSI_HD double natanh(double x) { return ::atanh(x); }
+NUSI_HD double nhypot(double x, double y) { return ::hypot(x, y); }
 #endif
 
 static const double kPi = 3.14159265358979323846264338328;
@@ -89,9 +106,9 @@ NUSI_HD cplx operator/(cplx a, cplx b) {
 }
 NUSI_HD cplx operator/(double s, cplx b) { return mk(s, 0.0) / b; }
 NUSI_HD cplx conj(cplx a) { return mk(a.re, -a.im); }
-NUSI_HD double cabs_(cplx a) { return hypot(a.re, a.im); }
+NUSI_HD double cabs_(cplx a) { return nhypot(a.re, a.im); }
 NUSI_HD double carg_(cplx a) { return natan2(a.im, a.re); }
-NUSI_HD cplx clog_(cplx a) { return mk(nlog(hypot(a.re, a.im)), natan2(a.im, a.re)); }
+NUSI_HD cplx clog_(cplx a) { return mk(nlog(nhypot(a.re, a.im)), natan2(a.im, a.re)); }
 NUSI_HD cplx csqr(cplx a) { return a * a; }
 NUSI_HD cplx ccub(cplx a) { return a * a * a; }
 

@@ -61,9 +61,41 @@ static inline double _Complex nusi_ulpc(double _Complex v) { return nusi_ulp(cre
 #define cabs(x) nusi_ulp(cabs(x))
 #define clog(x) nusi_ulpc(clog(x))
 #endif
+#ifdef NUSI_REF_LOCKED
+// The libm-locked oracle O2: the same unmodified reference, with every log / log1p / atan / atanh /
+// carg / cabs / clog of its own code routed to nusiprop_b200/csrc/nusi_locked_math.h (IEEE basic operations only: the
+// same bits on the host and on the GPU) and the two GSL dilogarithms served by the product's Li2 (REFSHIM_SHARED_LI2).
+// Compared with the product's own locked build, what remains is the product's arithmetic, not libm noise.
+#include <gsl/gsl_linalg.h>
+#include <gsl/gsl_sf_dilog.h>
+#include <gsl/gsl_poly.h>
+#include "polylogarithm/src/cpp/Li2.hpp"
+#include "polylogarithm/src/cpp/Li3.hpp"
+#include <complex.h>
+#include "../nusiprop_b200/csrc/nusi_locked_math.h"
+static inline double _Complex nusi_lk_clog(double _Complex v) {
+  return nusi_locked::log(nusi_locked::hypot(creal(v), cimag(v))) + I * nusi_locked::atan2(cimag(v), creal(v));
+}
+#define log(x) nusi_locked::log(x)
+#define log1p(x) nusi_locked::log1p(x)
+#define atan(x) nusi_locked::atan(x)
+#define atanh(x) nusi_locked::atanh(x)
+#define carg(x) nusi_locked::atan2(cimag(x), creal(x))
+#define cabs(x) nusi_locked::hypot(creal(x), cimag(x))
+#define clog(x) nusi_lk_clog(x)
+#endif
 #define private public
 #include "nuSIprop.hpp"
 #undef private
+#ifdef NUSI_REF_LOCKED
+#undef log
+#undef log1p
+#undef atan
+#undef atanh
+#undef carg
+#undef cabs
+#undef clog
+#endif
 #ifdef NUSI_REF_ULP
 #undef log
 #undef log1p

@@ -204,6 +204,24 @@ inline cplx cdilog_xy(double x, double y) {
 }
 }  // namespace refshim_gsl
 
+#ifdef REFSHIM_SHARED_LI2
+// The libm-locked oracle (oracle/_ref/libnusi_ref_locked.so): the two GSL entry points are served by
+// the PRODUCT's own Li2 (nusiprop_b200/csrc/nusi_math.h compiled for the host, its logarithms and arguments from
+// nusi_locked_math.h), so that this build and the product's locked build share every transcendental and differ only
+// where the product's arithmetic differs from the reference's.  Not an independent check of Li2 (that is the default
+// stand-in above, pinned to mpmath); a check of everything else.
+#ifndef NUSI_LOCKED_MATH
+#define NUSI_LOCKED_MATH
+#endif
+#include "../../../nusiprop_b200/csrc/nusi_math.h"
+inline double gsl_sf_dilog(const double x) { return nusi::li2_real(x); }
+inline int gsl_sf_complex_dilog_xy_e(const double x, const double y, gsl_sf_result *re, gsl_sf_result *im) {
+  const nusi::cplx v = nusi::cli2(x, y);
+  re->val = v.re; re->err = 0.0;
+  im->val = v.im; im->err = 0.0;
+  return 0;
+}
+#else
 inline double gsl_sf_dilog(const double x) { return refshim_gsl::dilog(x); }
 inline int gsl_sf_complex_dilog_xy_e(const double x, const double y, gsl_sf_result *re, gsl_sf_result *im) {
   const refshim_gsl::cplx v = refshim_gsl::cdilog_xy(x, y);
@@ -211,4 +229,5 @@ inline int gsl_sf_complex_dilog_xy_e(const double x, const double y, gsl_sf_resu
   im->val = v.imag(); im->err = 0.0;
   return 0;
 }
+#endif
 #endif

@@ -110,11 +110,11 @@ def evolve(mphi, g, mntot, si=2.0, norm=1.0, majorana=True, non_resonant=True, n
     return fm, ff, en
 
 
-def grid(N_bins_E, lEmin, lEmax, zmax):
+def grid(N_bins_E, lEmin, lEmax, zmax, variant=""):
     N = int(N_bins_E)
     nz = I()
     Emin, Emax, Ec, z = np.zeros(N), np.zeros(N), np.zeros(N), np.zeros(100000)
-    lib().nusi_ref_grid(N, lEmin, lEmax, zmax, C.byref(nz), _p(Emin), _p(Emax), _p(Ec), _p(z))
+    lib(variant).nusi_ref_grid(N, lEmin, lEmax, zmax, C.byref(nz), _p(Emin), _p(Emax), _p(Ec), _p(z))
     return nz.value, Emin, Emax, Ec, z[: nz.value].copy()
 
 
