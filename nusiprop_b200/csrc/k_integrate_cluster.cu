@@ -565,7 +565,7 @@ cudaError_t launch_integrate_cluster(const IntegArgs &A, int variant, cudaStream
   const int dbg = variant >= 20 ? variant - 20 : 0;
   if (need <= NUSI_CL_C * 32 * 4) return launch_cluster_t<4, 4, 2>(A, s, dbg);
   if (need <= NUSI_CL_C * 32 * 8) return launch_cluster_t<4, 8, 2>(A, s, dbg);
-  if (need <= NUSI_CL_C * 32 * 16) return launch_cluster_t<4, 16, 2>(A, s, dbg);
+  if (need <= NUSI_CL_C * 32 * 16) return variant == 11 ? launch_cluster_t<4, 16, 1>(A, s, 0) : launch_cluster_t<4, 16, 2>(A, s, dbg);
   return cudaErrorInvalidValue;
 }
 

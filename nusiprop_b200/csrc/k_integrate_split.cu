@@ -31,7 +31,7 @@
 namespace nusi {
 
 #ifndef NUSI_SPLIT_MAXREG
-#define NUSI_SPLIT_MAXREG 96  // 10 warps per CTA, 2 CTAs per SM: 5 warps per scheduler x 32 x 96 = 15360 of its 16384 registers
+#define NUSI_SPLIT_MAXREG 96  // 9 warps per CTA (critical, helper, 7 bulk), 2 CTAs per SM (112 registers: 5.9 instead of 3.55 ms per 8192 points)
 #endif
 #define NUSI_SPLIT_PF 12  // slot fields: lum, offdiag, Gam, aT, Z0, rZ0, Z1, rZ1, Z2, rZ2, dE, 1/dE
 #define NUSI_SPLIT_RB 5   // ring depth in blocks of B columns (block kb-1 .. kb+3)
@@ -265,27 +265,24 @@ __device__ __forceinline__ void split_help_block(double *ssm, const SplitCtx &C,
     }
   }
 }
-// column of wave w_rel: c = NT-1-(s0+w_rel); rows 0..c-1 at packed offset c(c-1)/2.  Issue block kb's B columns (one thread).
+// column of wave w_rel: c = NT-1-(s0+w_rel); rows 0..c-1 at packed offset c(c-1)/2.  Issue block kb's B columns: called by a
+// WHOLE warp, lane r (< B) copies column r, lane 0 announces the byte count first.  (No proxy fence per block: the ring slot's
+// last readers are ordered before this call by the block barrier, as in any consumer-release / producer-refill pipeline.)
 template <int B>
-__device__ __forceinline__ void split_issue_block(const SplitCtx &C, int kb) {
+__device__ __forceinline__ void split_issue_block(const SplitCtx &C, int kb, int lane) {
   const int rb = kb % NUSI_SPLIT_RB;
   const unsigned bar = C.mbar0 + 8u * rb;
-  unsigned total = 0;
-#pragma unroll
-  for (int r = 0; r < B; ++r) {
-    const int w_rel = kb * B + r, c = C.NT - 1 - (C.s0 + w_rel);
-    if (w_rel < C.n_waves && c > 0) total += (unsigned)((split_mis(C.tpar, c) + c + 1) & ~1) * 8u;
+  const int r = lane, w_rel = kb * B + r, c = C.NT - 1 - (C.s0 + w_rel);
+  unsigned bytes = 0;
+  int mis = 0;
+  if (r < B && w_rel < C.n_waves && c > 0) {
+    mis = split_mis(C.tpar, c);
+    bytes = (unsigned)((mis + c + 1) & ~1) * 8u;
   }
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // earlier generic-proxy reads of the slots are ordered before the async writes
-  mbar_expect_tx(bar, total);
-#pragma unroll
-  for (int r = 0; r < B; ++r) {
-    const int w_rel = kb * B + r, c = C.NT - 1 - (C.s0 + w_rel);
-    if (w_rel < C.n_waves && c > 0) {
-      const int mis = split_mis(C.tpar, c);
-      tma_bulk_g2s(C.ring0 + (unsigned)((rb * B + r) * C.NTP) * 8u, C.T + (size_t)c * (c - 1) / 2 - mis, (unsigned)((mis + c + 1) & ~1) * 8u, bar);
-    }
-  }
+  const unsigned total = __reduce_add_sync(0xffffffffu, bytes);
+  if (lane == 0) mbar_expect_tx(bar, total);
+  __syncwarp();
+  if (bytes) tma_bulk_g2s(C.ring0 + (unsigned)((rb * B + r) * C.NTP) * 8u, C.T + (size_t)c * (c - 1) / 2 - mis, bytes, bar);
 }
 template <int B, int NHW, int NTHR>
 static __device__ __noinline__ void split_helper(double *ssm) {
@@ -296,7 +293,7 @@ static __device__ __noinline__ void split_helper(double *ssm) {
   split_help_load<B, NHW>(C, 1, hw, lane, hs);
   split_help_load<B, NHW>(C, 2, hw, lane, hsn);
   for (int kb = 0; kb < n_blocks; ++kb) {
-    if (threadIdx.x == 32 && kb + 3 < n_blocks) split_issue_block<B>(C, kb + 3);
+    if (hw == 0 && kb + 3 < n_blocks) split_issue_block<B>(C, kb + 3, lane);
     if (kb + 1 < n_blocks) split_help_block<B, NHW>(ssm, C, kb + 1, hw, lane, hs);
 #pragma unroll
     for (int q = 0; q < RH; ++q) hs[q] = hsn[q];
@@ -410,6 +407,7 @@ integrate_split_kernel(DeviceGrid G, const PointParams *__restrict__ params, con
     fband[i] = fband[NP + i] = fband[2 * NP + i] = 0.0;
   }
   for (int i = NUSI_SPLIT_CTX_DOUBLES + tid; i < L.ring; i += NTHR) ssm[i] = 0.0;  // the pad in front of the ring
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the ring is written by the async proxy from here on
   if (tid == 0) {
 #pragma unroll
     for (int i = 0; i < NUSI_SPLIT_RB; ++i) mbar_init(mbar0 + 8u * i, 1);
@@ -438,8 +436,8 @@ integrate_split_kernel(DeviceGrid G, const PointParams *__restrict__ params, con
     }
     for (int i = tid; i < 2 * B * 32; i += NTHR) ssm[L.ash + i] = 0.0;
     __syncthreads();
-    if (tid == 32) {  // TMA producer: first helper warp, lane 0
-      for (int kb = 0; kb < 3 && kb < n_blocks; ++kb) split_issue_block<B>(C, kb);
+    if (warp == 1) {  // TMA producer: first helper warp, one lane per column
+      for (int kb = 0; kb < 3 && kb < n_blocks; ++kb) split_issue_block<B>(C, kb, tid & 31);
     }
     if (warp >= 1 && warp <= NHW) {
       double hs0[(B + NHW - 1) / NHW];
@@ -486,9 +484,9 @@ static cudaError_t launch_split_t(const IntegArgs &A, cudaStream_t s, int dbg = 
 // variant: tuning experiments (opts.fine_variant 10..); 0 = the product configuration
 cudaError_t launch_integrate_split(const IntegArgs &A, int variant, cudaStream_t s) {
   switch (variant) {
-    case 11: return launch_split_t<4, 7, 1>(A, s);
-    case 13: return launch_split_t<2, 7, 2>(A, s);
-    default: return launch_split_t<4, 7, 2>(A, s, variant >= 20 ? variant - 20 : 0);  // 20 + bits: timing experiments (1 no bulk, 2 no critical, 4 no helper)
+    case 11: return launch_split_t<4, 7, 2>(A, s);  // two helper warps: 4.02 ms per 8192 points against 3.57 (the tenth warp costs more than it prepares)
+    case 13: return launch_split_t<2, 7, 1>(A, s);
+    default: return launch_split_t<4, 7, 1>(A, s, variant >= 20 ? variant - 20 : 0);  // 20 + bits: timing experiments (1 no bulk, 2 no critical)
   }
 }
 

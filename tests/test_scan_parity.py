@@ -87,3 +87,30 @@ def test_scan_runner_is_the_product_path_and_equals_context_evolve_bitwise(nusi)
     ctx.close()
     fm, ff, st = evolve_scan_distributed(mphi[:300], g[:300], 0.1, ctx_kwargs=CFG200)
     assert np.array_equal(fm, ref[0][:300]) and np.array_equal(ff, ref[1][:300])
+
+
+@pytest.mark.gpu
+def test_fast_builder_against_the_strict_builder_on_a_full_shard(nusi):
+    """Breadth beyond the 1024-point fixture: elementary_mode 0 is the reference's arithmetic (bit-identical tables and
+    fluxes within 7e-15 of the libm-locked oracle, tests/test_locked_parity.py), so the default builder can be measured
+    against it on EVERY point of a shard of the headline scan.  The tiers must look like the fixture's: well over 90 % of the
+    bins within 1e-9, nothing off by more than a few per cent, and the large deviations only where the reference is
+    ill-conditioned (m_phi >~ 1e3 eV with g >~ 1e-2: there two builds of the reference differ by up to 2.5e-2)."""
+    import bench
+    mphi, g = bench.shard(5)
+    ctx = nusi.Context(**CFG200)
+    fast = ctx.evolve(mphi, g, 0.1)
+    ctx.close()
+    ctx = nusi.Context(elementary_mode=0, **CFG200)
+    strict = ctx.evolve(mphi, g, 0.1)
+    ctx.close()
+    assert np.array_equal(fast[2] & ~7, strict[2] & ~7) and np.isfinite(fast[0]).all() and np.isfinite(strict[0]).all()
+    r = SP.relerr(fast[0], strict[0]).max(axis=(1, 2))  # per point
+    rb = SP.relerr(fast[0], strict[0]).max(axis=1)      # per (point, bin)
+    for lo, hi in ((10, 1e2), (1e2, 1e3), (1e3, 1e4 + 1)):
+        m = (mphi >= lo) & (mphi < hi)
+        print("mode 3 vs mode 0, %g <= m_phi < %g eV: %d points, bins within 1e-9 %.4f, worst %.2e" % (lo, hi, m.sum(), np.mean(rb[m] <= 1e-9), r[m].max()))
+    print("all 8192 points: bins within 1e-9 %.4f, worst %.2e at (%.1f, %.2e)" % (np.mean(rb <= 1e-9), r.max(), mphi[np.argmax(r)], g[np.argmax(r)]))
+    assert np.mean(rb <= 1e-9) > 0.92
+    assert r.max() < 0.05
+    assert r[mphi < 1e2].max() < 1e-9  # the well-conditioned third of the scan: north_star's tolerance with no floor term

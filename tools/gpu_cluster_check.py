@@ -59,7 +59,7 @@ for N in sizes:
 
 # role ablation at N_E = 2000 (timing switches, wrong results): where a block's time goes
 if 2000 in sizes:
-    for var in (0, 21, 22, 23, 27, 31, 35):
+    for var in (0, 11, 21, 22, 23):
         ctx = nb.Context(integrator=4, fine_variant=var, N_bins_E=2000, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
         for _ in range(2):
             ctx.evolve([100.0], [1e-2], 0.1)
