@@ -341,7 +341,7 @@ def bench_cuda(args):
     h_fm = torch.empty((n, 3, N_E), dtype=torch.float64, pin_memory=True).numpy()
     h_ff = torch.empty((n, 3, N_E), dtype=torch.float64, pin_memory=True).numpy()
     from nusiprop_b200.api import _dp, _ip
-    h_st = np.zeros(n, dtype=np.int32)
+    h_st = torch.zeros(n, dtype=torch.int32, pin_memory=True).numpy()
     lib = ctx._lib
 
     def e2e_step():

@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define NUSI_ABI_VERSION 3
+#define NUSI_ABI_VERSION 4
 
 /* error codes (function return values) */
 #define NUSI_OK 0
@@ -77,7 +77,7 @@ typedef struct nusi_opts {
   double si;             /* spectral index, source_model 1 only (default 2; si == 1 is rejected: the bin integral of
                             :656 divides by 1 - si) */
   double norm;           /* free-streaming flux at Earth at E0, source_model 1 only (default 1) */
-  /* ---- switches of the implementation (ABI 3; all default 0 = the product path).  They select cross-check
+  /* ---- switches of the implementation (since ABI 3; host_copy: ABI 4; all default 0 = the product path).  They select cross-check
    *      kernels and tuning variants that produce the same numbers; tests and tools set them here, nothing in the
    *      library reads the environment. */
   int integrator;        /* 0 = default: role-split wavefront kernel, one CTA per point (32 <= N_bins_E <= 224) or one point over a
@@ -100,6 +100,11 @@ typedef struct nusi_opts {
                                 bit-identical to it) and uploaded; 1 = computed by the CUDA source kernel (device exp / log
                                 + Li2 / Li3; differs from the host array by up to 1e-6 in the four lowest bins, where the
                                 difference of antiderivatives cancels) */
+  int host_copy;         /* nusi_evolve_batch, device -> host copies of the results: 0 = default, slice by slice on a copy stream
+                                under the kernels of the next slice (21.9 ms per 8192 points on B200, device-resident 21.1);
+                            1 = after the last kernel (22.9 ms).  A page-locked caller buffer (cudaHostAlloc / cudaHostRegister,
+                                detected per array) is written by the copy engine directly; a pageable one goes through the
+                                context's page-locked staging area and a memcpy (78 MB per 8192 points: +2 ms) */
 } nusi_opts;
 
 /* Fills *o with the reference's C++ constructor defaults (nuSIprop.hpp:61-65). */

@@ -31,7 +31,7 @@ class NusiOpts(C.Structure):
         ("source_model", C.c_int),
         ("si", C.c_double),
         ("norm", C.c_double),
-        # implementation switches (ABI 3): cross-check kernels and tuning variants, all default 0
+        # implementation switches (ABI 3, host_copy ABI 4): cross-check kernels and tuning variants, all default 0
         ("integrator", C.c_int),
         ("fine_variant", C.c_int),
         ("builder_per_entry", C.c_int),
@@ -42,11 +42,12 @@ class NusiOpts(C.Structure):
         ("keep_order", C.c_int),
         ("two_stream", C.c_int),
         ("source_device", C.c_int),
+        ("host_copy", C.c_int),
     ]
 
 
 SWITCHES = ("integrator", "fine_variant", "builder_per_entry", "group_max", "group_always", "rows_split", "rows_ungrouped", "keep_order",
-            "two_stream", "source_device")
+            "two_stream", "source_device", "host_copy")
 
 
 # name -> (restype, argtypes); also the list tests check against the header

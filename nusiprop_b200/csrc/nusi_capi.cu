@@ -794,10 +794,13 @@ static int slice_event(std::vector<cudaEvent_t> &v, size_t k, cudaEvent_t *out) 
 struct HostOut {
   double *fm = nullptr, *ff = nullptr;
   int *st = nullptr;
-  bool direct = false;
+  // per array: the caller's buffer is page-locked (the copy engine writes it directly), or it is pageable and the copy goes
+  // through the context's page-locked staging area followed by a memcpy
+  bool fm_direct = true, ff_direct = true, st_direct = true;
   double *s_fm = nullptr, *s_ff = nullptr;  // staging (whole batch, same indexing as the destinations)
   int *s_st = nullptr;
   bool any() const { return fm || ff || st; }
+  bool staged() const { return (fm && !fm_direct) || (ff && !ff_direct) || (st && !st_direct); }
 };
 
 // d_fm / d_ff / d_st: device outputs indexed by the caller's point index.
@@ -830,12 +833,12 @@ static int run_pipeline(nusi_ctx *c, const nusi_points *p, double *d_fm, double 
     CU(cudaEventRecord(c->ev_ji, si));
     CU(cudaStreamWaitEvent(sx, c->ev_ji, 0));
   }
-  const bool per_slice_copy = to_host && !p->reordered;
+  const bool per_slice_copy = to_host && !p->reordered && c->opt.host_copy == 0;
   auto copy_piece = [&](int off, int cnt, size_t k) -> int {  // outputs [off, off + cnt) (caller order) -> host
     const size_t o = (size_t)off * 3 * N, b = (size_t)cnt * 3 * N * sizeof(double);
-    if (ho->fm) CU(cudaMemcpyAsync((ho->direct ? ho->fm : ho->s_fm) + o, d_fm + o, b, cudaMemcpyDeviceToHost, sc));
-    if (ho->ff) CU(cudaMemcpyAsync((ho->direct ? ho->ff : ho->s_ff) + o, d_ff + o, b, cudaMemcpyDeviceToHost, sc));
-    if (ho->st) CU(cudaMemcpyAsync((ho->direct ? ho->st : ho->s_st) + off, d_st + off, (size_t)cnt * sizeof(int), cudaMemcpyDeviceToHost, sc));
+    if (ho->fm) CU(cudaMemcpyAsync((ho->fm_direct ? ho->fm : ho->s_fm) + o, d_fm + o, b, cudaMemcpyDeviceToHost, sc));
+    if (ho->ff) CU(cudaMemcpyAsync((ho->ff_direct ? ho->ff : ho->s_ff) + o, d_ff + o, b, cudaMemcpyDeviceToHost, sc));
+    if (ho->st) CU(cudaMemcpyAsync((ho->st_direct ? ho->st : ho->s_st) + off, d_st + off, (size_t)cnt * sizeof(int), cudaMemcpyDeviceToHost, sc));
     cudaEvent_t evc;
     int r = slice_event(c->ev_copied, k, &evc);
     if (r) return r;
@@ -904,15 +907,15 @@ static int run_pipeline(nusi_ctx *c, const nusi_points *p, double *d_fm, double 
     for (int off = 0; off < p->n; off += SL, ++npieces)
       if ((rc = copy_piece(off, std::min(SL, p->n - off), npieces))) return rc;
   }
-  if (to_host && !ho->direct) {  // staging -> the caller's pageable buffers, piece by piece as the copies complete
+  if (to_host && ho->staged()) {  // staging -> the caller's pageable buffers, piece by piece as the copies complete
     size_t q = 0;
     for (int off = 0; off < p->n; off += SL, ++q) {
       const int cnt = std::min(SL, p->n - off);
       CU(cudaEventSynchronize(c->ev_copied[q]));
       const size_t o = (size_t)off * 3 * N, b = (size_t)cnt * 3 * N * sizeof(double);
-      if (ho->fm) std::memcpy(ho->fm + o, ho->s_fm + o, b);
-      if (ho->ff) std::memcpy(ho->ff + o, ho->s_ff + o, b);
-      if (ho->st) std::memcpy(ho->st + off, ho->s_st + off, (size_t)cnt * sizeof(int));
+      if (ho->fm && !ho->fm_direct) std::memcpy(ho->fm + o, ho->s_fm + o, b);
+      if (ho->ff && !ho->ff_direct) std::memcpy(ho->ff + o, ho->s_ff + o, b);
+      if (ho->st && !ho->st_direct) std::memcpy(ho->st + off, ho->s_st + off, (size_t)cnt * sizeof(int));
     }
   }
   if (to_host) {
@@ -966,8 +969,10 @@ int nusi_evolve_batch(nusi_ctx *c, int n, const double *mphi, const double *g, c
   ho.fm = flux_mass;
   ho.ff = flux_fla;
   ho.st = status;
-  ho.direct = is_pinned(flux_mass) && is_pinned(flux_fla) && is_pinned(status);
-  if (ho.any() && !ho.direct) {
+  ho.fm_direct = is_pinned(flux_mass);
+  ho.ff_direct = is_pinned(flux_fla);
+  ho.st_direct = is_pinned(status);
+  if (ho.staged()) {
     const size_t bf = (size_t)n * 3 * N * sizeof(double), need = 2 * bf + (size_t)n * sizeof(int);
     if (need > c->h_stage_cap) {
       if (c->h_stage) cudaFreeHost(c->h_stage);

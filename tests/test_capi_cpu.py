@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol(nusi):
     for name in sorted(declared):
         assert hasattr(lib, name), "symbol %s declared in include/nusiprop_b200.h but not exported" % name
     assert declared == set(_lib.SIGNATURES), "ctypes table and header disagree: %s" % (declared ^ set(_lib.SIGNATURES))
-    assert _lib.load().nusi_abi_version() == 3
+    assert _lib.load().nusi_abi_version() == 4
 
 
 def test_opts_defaults_match_reference_constructor(nusi):
