@@ -6,6 +6,10 @@
 
 namespace nusi {
 
+#ifndef NUSI_ROWS_MINB
+#define NUSI_ROWS_MINB 4  // resident CTAs of 192 threads per SM the row kernels are compiled for (80 registers)
+#endif
+
 // ------------------------------------------------------------------------------------------
 // cross-section builder, straightforward form: one thread per table row / per table entry
 // ------------------------------------------------------------------------------------------
@@ -16,7 +20,7 @@ namespace nusi {
 // (large) code body, which keeps it in the instruction cache -- with both functions in one CTA the kernel
 // spent most of its time in instruction-fetch stalls.
 template <int WHICH>
-__global__ void __launch_bounds__(NUSI_ROWS_PER_CTA * 3, 4)
+__global__ void __launch_bounds__(NUSI_ROWS_PER_CTA * 3, NUSI_ROWS_MINB)
 rows_kernel(DeviceGrid G, const PointParams *__restrict__ params, double *__restrict__ rows, int *__restrict__ status) {
   __shared__ double ch[NUSI_ROWS_PER_CTA][3][NUSI_ATILDE_NCH + 1];
   __shared__ int nch;
@@ -50,7 +54,7 @@ rows_kernel(DeviceGrid G, const PointParams *__restrict__ params, double *__rest
 // and most logarithms), then loops over the points of the group with the per-point rest (Breit-Wigner terms,
 // complex dilogarithms, args).  Same bits as rows_kernel (split functions, asserted in the tests).
 template <int WHICH>
-__global__ void __launch_bounds__(NUSI_ROWS_PER_CTA * 3, 4)
+__global__ void __launch_bounds__(NUSI_ROWS_PER_CTA * 3, NUSI_ROWS_MINB)
 rows_group_kernel(DeviceGrid G, const PointParams *__restrict__ params, const int2 *__restrict__ groups,
                   double *__restrict__ rows, int *__restrict__ status) {
   constexpr int NCH = (WHICH == 0) ? NUSI_GAMMA_NCH : NUSI_ATILDE_NCH;

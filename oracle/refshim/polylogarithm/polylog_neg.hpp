@@ -6,7 +6,7 @@
 // polylogarithm::Li2 / Li3 only from Lum_int (nuSIprop.hpp:628-646) with
 // argument -exp(-x) in [-1, 0].  We evaluate x * Chebyshev(Li_n(x)/x), table
 // generated with mpmath by tools/gen_polylog_coeffs.py; accuracy <= 2e-16
-// relative on [-1, 0] (tests/test_specfun_host.py pins it against mpmath).
+// relative on [-1, 0] (tests/test_oracle_cpu.py and tests/test_host_math.py pin it against mpmath: tests/golden/specfun_mpmath.json).
 #ifndef REFSHIM_POLYLOG_NEG_HPP
 #define REFSHIM_POLYLOG_NEG_HPP
 #include <cstdio>
