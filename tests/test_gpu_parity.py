@@ -515,3 +515,35 @@ def test_fine_binning_config_at_full_size(nusi):
         print("N_E=2000: worst rel %.2e (mass) %.2e (flavour), %d bins excused by the floor" % (rm.max(), rf.max(), int((rm.max(axis=0) > 1e-9).sum())))
     assert ctx.last_grouping()["n_grouped_points"] == 5
     ctx.close()
+
+
+def test_host_buffers_pinned_or_pageable_per_array_same_bits(nusi):
+    """nusi_evolve_batch writes a page-locked caller buffer directly and stages a pageable one (detected per array), slice
+    by slice under the next slice's kernels (host_copy 0) or after the last kernel (1): every combination returns the bits
+    of the device-resident path, including a ragged last slice."""
+    import ctypes as C
+    import torch
+    from nusiprop_b200.api import _dp, _ip
+    n = 2048 + 700
+    mphi, g = _scan_sample(n, 21)
+    mphi, g = np.sort(mphi), g  # rows of equal mphi do not occur: per-point builder, any order
+    mntot = np.full(n, 0.1)
+    cfg = dict(N_bins_E=64, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
+    ref = None
+    for host_copy in (0, 1):
+        ctx = nusi.Context(host_copy=host_copy, **cfg)
+        if ref is None:
+            ref = ctx.evolve(mphi, g, mntot)  # numpy outputs: all three pageable
+        N = ctx.N_bins_E
+        for pin in ((1, 1, 1), (1, 1, 0), (0, 1, 1), (1, 0, 0)):
+            fm = torch.empty((n, 3, N), dtype=torch.float64, pin_memory=bool(pin[0])).numpy()
+            ff = torch.empty((n, 3, N), dtype=torch.float64, pin_memory=bool(pin[1])).numpy()
+            st = torch.empty(n, dtype=torch.int32, pin_memory=bool(pin[2])).numpy()
+            fm[:], ff[:], st[:] = -1.0, -1.0, -1
+            assert ctx._lib.nusi_evolve_batch(ctx._h, n, _dp(mphi), _dp(g), _dp(mntot), _dp(fm), _dp(ff), _ip(st)) == 0
+            assert np.array_equal(fm, ref[0], equal_nan=True) and np.array_equal(ff, ref[1], equal_nan=True) and np.array_equal(st, ref[2]), (host_copy, pin)
+        # one output only
+        ff = torch.empty((n, 3, N), dtype=torch.float64, pin_memory=True).numpy()
+        assert ctx._lib.nusi_evolve_batch(ctx._h, n, _dp(mphi), _dp(g), _dp(mntot), None, _dp(ff), None) == 0
+        assert np.array_equal(ff, ref[1], equal_nan=True)
+        ctx.close()
