@@ -547,3 +547,32 @@ def test_host_buffers_pinned_or_pageable_per_array_same_bits(nusi):
         assert ctx._lib.nusi_evolve_batch(ctx._h, n, _dp(mphi), _dp(g), _dp(mntot), None, _dp(ff), None) == 0
         assert np.array_equal(ff, ref[1], equal_nan=True)
         ctx.close()
+
+
+def test_cluster_integrator_with_rejected_points_and_reordering(nusi):
+    """The cluster kernel (N_E >= 640) behind the same host logic as the others: rejected points (NaN fluxes, status bit, no
+    effect on their neighbours), a shuffled scan that the library regroups and scatters back, a ragged batch."""
+    cfg = dict(N_bins_E=700, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
+    rng = np.random.default_rng(3)
+    mphi = np.repeat([30.0, 300.0, 3000.0], 9)
+    g = np.tile(10 ** np.linspace(-4, -1, 9), 3)
+    perm = rng.permutation(mphi.size)
+    mphi, g = mphi[perm], g[perm]
+    mntot = np.full(mphi.size, 0.1)
+    bad = [2, 11, 20]
+    mphi_b, g_b, mn_b = mphi.copy(), g.copy(), mntot.copy()
+    mphi_b[bad[0]], g_b[bad[1]], mn_b[bad[2]] = -5.0, np.inf, 1e-9  # non-positive mass, non-finite coupling, no mass spectrum
+    ctx = nusi.Context(**cfg)
+    ref = nusi.Context(integrator=3, **cfg)
+    a = ctx.evolve(mphi_b, g_b, mn_b)
+    assert ctx.last_grouping()["reordered"]
+    b = ref.evolve(mphi_b, g_b, mn_b)
+    clean = ctx.evolve(mphi, g, mntot)
+    ctx.close()
+    ref.close()
+    ok = np.ones(mphi.size, dtype=bool)
+    ok[bad] = False
+    assert np.isnan(a[0][bad]).all() and np.isnan(a[1][bad]).all() and np.all(a[2][bad] & (256 | 512))
+    assert np.array_equal(a[2], b[2]) and np.isfinite(a[0][ok]).all()
+    assert np.array_equal(a[0][ok], clean[0][ok]) and np.array_equal(a[1][ok], clean[1][ok])  # neighbours untouched, bit for bit
+    assert np.all(np.abs(a[0][ok] - b[0][ok]) <= 1e-14 * np.abs(b[0][ok]) + 1e-300)
