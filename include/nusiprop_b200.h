@@ -95,7 +95,9 @@ typedef struct nusi_opts {
   int keep_order;        /* 1 = do not reorder a batch: by default the points are sorted by (mphi, mntot) before the
                                 groups are cut, so the scan builder's gain does not depend on the caller's order;
                                 results always come back in the caller's order */
-  int two_stream;        /* 1 = builder and rows + integrator on two streams (measured neutral on B200) */
+  int two_stream;        /* 1 = builder and rows + integrator on two streams: the integrator of a slice runs beside the builder
+                                of the next one (r02: 20.63 instead of 21.01 ms per 8192 points, same bits; not the default
+                                because per-kernel event times then overlap and no longer add up to the step) */
   int source_device;     /* source_model 0: 0 = Lum(z_i, bin j) computed on the host (same glibc calls as the reference,
                                 bit-identical to it) and uploaded; 1 = computed by the CUDA source kernel (device exp / log
                                 + Li2 / Li3; differs from the host array by up to 1e-6 in the four lowest bins, where the

@@ -441,8 +441,11 @@ NUSI_GK_UNROLL
   }
 }
 
+#ifndef NUSI_GROUP_SMEM_PAD
+#define NUSI_GROUP_SMEM_PAD 0  // tuning experiments: extra dynamic shared memory per CTA, to cap the resident CTAs per SM
+#endif
 cudaError_t alpha_setup_attributes() {
-  return cudaFuncSetAttribute(alpha_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GroupSmem));
+  return cudaFuncSetAttribute(alpha_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(GroupSmem) + NUSI_GROUP_SMEM_PAD);
 }
 size_t alpha_group_smem_bytes() { return sizeof(GroupSmem); }
 cudaError_t launch_edges(const BuildArgs &A, cudaStream_t s) {
@@ -453,7 +456,7 @@ cudaError_t launch_edges(const BuildArgs &A, cudaStream_t s) {
 }
 cudaError_t launch_alpha_group(const BuildArgs &A, cudaStream_t s) {
   dim3 gg(A.n_ctiles, A.ngroups);
-  alpha_group_kernel<<<gg, 256, sizeof(GroupSmem), s>>>(A.G, A.nE, A.params, A.edges, A.ctiles, A.groups, A.tri, A.tstride, A.status);
+  alpha_group_kernel<<<gg, 256, sizeof(GroupSmem) + NUSI_GROUP_SMEM_PAD, s>>>(A.G, A.nE, A.params, A.edges, A.ctiles, A.groups, A.tri, A.tstride, A.status);
   return cudaGetLastError();
 }
 cudaError_t launch_alpha_compact(const BuildArgs &A, cudaStream_t s) {
