@@ -80,8 +80,8 @@ typedef struct nusi_opts {
   /* ---- switches of the implementation (since ABI 3; host_copy: ABI 4; all default 0 = the product path).  They select cross-check
    *      kernels and tuning variants that produce the same numbers; tests and tools set them here, nothing in the
    *      library reads the environment. */
-  int integrator;        /* 0 = default: role-split wavefront kernel, one CTA per point (32 <= N_bins_E <= 224) or one point over a
-                                thread-block cluster of 4 CTAs (640 <= N_bins_E <= 2017); diagonal-owned wavefront kernel otherwise;
+  int integrator;        /* 0 = default: role-split wavefront kernel, one CTA per point (32 <= N_bins_E <= 576) or one point over a
+                                thread-block cluster of 4 CTAs (577 <= N_bins_E <= 2017); diagonal-owned wavefront kernel otherwise;
                             1 = bin-owned wavefront kernel (cross-check);
                             2 = serial, reference-shaped bin-by-bin kernel with true divisions (cross-check, N_bins_E <= 256);
                             3 = diagonal-owned wavefront kernel at every binning;

@@ -1,4 +1,5 @@
-// k_integrate_split.cu -- the implicit z-stepping integrator (reference nuSIprop.hpp:255-336), role-split wavefront.
+// k_integrate_split.cu -- the implicit z-stepping integrator (reference nuSIprop.hpp:255-336), role-split wavefront, one CTA per
+// point: the product kernel for 32 <= N_bins_E <= 576.
 // (sm_100a, FP64 pipe; compiled -fmad=false: contraction only where fma() is written)
 //
 // Same wavefront as integrate_diag_kernel (cell (z-step s, bin m) on wave w = s + (N-1-m); all z-steps of a wave
@@ -467,7 +468,8 @@ integrate_split_kernel(DeviceGrid G, const PointParams *__restrict__ params, con
   if (status_out && tid == 0) status_out[q] = status_in[p];
 }
 
-bool integrate_split_supports(int N, int NT) { return N >= 32 && N <= 224 && NT <= 512; }
+// 7 bulk warps (two CTAs per SM) up to N_bins_E = 224; 12 and 18 bulk warps (one CTA per SM: 14 / 20 warps x 96 registers) up to 384 / 576
+bool integrate_split_supports(int N, int NT) { return N >= 32 && N <= 576 && NT <= 704; }
 
 template <int B, int NBW, int NHW>
 static cudaError_t launch_split_t(const IntegArgs &A, cudaStream_t s, int dbg = 0) {
@@ -483,6 +485,10 @@ static cudaError_t launch_split_t(const IntegArgs &A, cudaStream_t s, int dbg = 
 
 // variant: tuning experiments (opts.fine_variant 10..); 0 = the product configuration
 cudaError_t launch_integrate_split(const IntegArgs &A, int variant, cudaStream_t s) {
+  // measured against the diagonal-owned kernel on B200 (tools/gpu_wide_check.py), 4096 points: N_E = 300: 9.8 vs 16.6 ms,
+  // 400: 13.8 vs 22.8, 500: 24.9 vs 60.5, 576: 28.2 vs 161.6; faster at every batch size from 8 points on
+  if (A.G.N > 384) return launch_split_t<4, 18, 1>(A, s);
+  if (A.G.N > 224) return launch_split_t<4, 12, 1>(A, s);
   switch (variant) {
     case 11: return launch_split_t<4, 7, 2>(A, s);  // two helper warps: 4.02 ms per 8192 points against 3.57 (the tenth warp costs more than it prepares)
     case 13: return launch_split_t<2, 7, 1>(A, s);

@@ -615,9 +615,9 @@ static int launch_integrate_stage(nusi_ctx *c, const IntegArgs &A, cudaStream_t 
     e = launch_integrate_wave(A, s);
   else if (c->opt.integrator == 0 && integrate_split_supports(c->G.N, c->G.NT))
     e = launch_integrate_split(A, c->opt.fine_variant, s);
-  // one point over a 4-CTA cluster: faster than the one-CTA kernel at every batch size from N_bins_E ~ 640 on (below, only for
-  // batches of <= 32 points; the choice depends on the binning alone so that a point's bits do not depend on its batch)
-  else if (((c->opt.integrator == 0 && c->G.N >= 640) || c->opt.integrator == 4) && integrate_cluster_supports(c->G.N, c->G.NT))
+  // beyond the one-CTA role-split kernel's reach (N_bins_E > 576: 20 warps x 96 registers fill the SM): one point over a 4-CTA
+  // cluster.  The choice depends on the binning alone, so that a point's bits do not depend on the size of its batch.
+  else if ((c->opt.integrator == 0 || c->opt.integrator == 4) && integrate_cluster_supports(c->G.N, c->G.NT))
     e = launch_integrate_cluster(A, c->opt.fine_variant, s);
   else
     e = launch_integrate_diag(A, c->opt.fine_variant, s);

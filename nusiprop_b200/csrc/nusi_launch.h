@@ -61,10 +61,10 @@ struct IntegArgs {
 // outside what the kernel family supports (N_bins_E <= 2041)
 cudaError_t launch_integrate_diag(const IntegArgs &A, int fine_variant, cudaStream_t s);
 bool integrate_diag_supports(int N, int NT);
-// k_integrate_split.cu -- product kernel for N_bins_E <= 225: role-split wavefront (critical warp / helpers / bulk warps, TMA ring)
+// k_integrate_split.cu -- product kernel for 32 <= N_bins_E <= 576: role-split wavefront (critical warp / helper / bulk warps, TMA ring)
 cudaError_t launch_integrate_split(const IntegArgs &A, int variant, cudaStream_t s);
 bool integrate_split_supports(int N, int NT);
-// k_integrate_cluster.cu -- product kernel for fine binnings (224 < N_bins_E <= 2017): the role-split wavefront with one point
+// k_integrate_cluster.cu -- product kernel for fine binnings (576 < N_bins_E <= 2017): the role-split wavefront with one point
 // spread over a thread-block cluster of 4 CTAs
 cudaError_t launch_integrate_cluster(const IntegArgs &A, int variant, cudaStream_t s);
 bool integrate_cluster_supports(int N, int NT);

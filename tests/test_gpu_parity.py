@@ -242,13 +242,14 @@ def test_wave_integrator_equals_serial_integrator_bitwise(nusi):
     assert np.array_equal(np.isnan(a[0]), np.isnan(c[0])) and np.all(np.abs(a[0][ok] - c[0][ok]) <= 1e-14 * np.abs(c[0][ok]) + 1e-300)
 
 
-@pytest.mark.parametrize("N_E", [300, 900, 1100])
+@pytest.mark.parametrize("N_E", [300, 450, 576, 900, 1100])
 def test_wide_integrator_configurations_equal_wave_kernel(nusi, N_E):
     """Finer binning.  The one-CTA-per-point kernel (opts.integrator = 3) runs 512 threads per point (N_E = 300, the class
     default: BPT 1, SB 32; 900: BPT 2, SB 16, DPT 3; 1100: BPT 4, SB 8, DPT 4, as N_E = 2000): same accumulation order as
-    the bin-owned wave kernel and as its 256-thread configurations (opts.fine_variant = 1).  The DEFAULT integrator for
-    N_E >= 640 is the cluster kernel (one point over 4 CTAs, role-split wavefront): a cell's regeneration sum is the sum of
-    two partial sums there, so it agrees with the others to rounding (a few ulp), not bit for bit."""
+    the bin-owned wave kernel and as its 256-thread configurations (opts.fine_variant = 1).  The DEFAULT integrators are the
+    role-split kernels (one CTA per point with 12 / 18 bulk warps up to N_E = 384 / 576, one point over a 4-CTA cluster
+    above): a cell's regeneration sum is the sum of two partial sums there, so they agree with the others to rounding (a
+    few ulp), not bit for bit."""
     mphi, g = _scan_sample(3, 11)
     cfg = dict(N_bins_E=N_E, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
     res = []
@@ -261,13 +262,14 @@ def test_wide_integrator_configurations_equal_wave_kernel(nusi, N_E):
     assert ok.any() and np.array_equal(np.isnan(a[0]), np.isnan(c[0])) and np.array_equal(np.isnan(d[0]), np.isnan(c[0]))
     assert np.array_equal(a[0], b[0], equal_nan=True) and np.array_equal(a[1], b[1], equal_nan=True)
     assert np.all(np.abs(a[0][ok] - c[0][ok]) <= 1e-14 * np.abs(c[0][ok]) + 1e-300)
-    # the default is the cluster kernel from N_E = 640 on (where it wins at every batch size; 4 selects it at any N_E > 224),
-    # the one-CTA kernel below: same zeros as the others, values to a few ulp
-    dflt = e if N_E >= 640 else a
-    assert np.array_equal(d[0], dflt[0], equal_nan=True) and np.array_equal(d[1], dflt[1], equal_nan=True) and np.array_equal(d[2], dflt[2])
-    assert np.array_equal(e[0] == 0, c[0] == 0) and np.array_equal(np.isnan(e[0]), np.isnan(c[0]))
-    assert np.all(np.abs(e[0][ok] - c[0][ok]) <= 1e-14 * np.abs(c[0][ok]) + 1e-300)
-    assert np.all(np.abs(e[1][ok] - c[1][ok]) <= 1e-14 * np.abs(c[1][ok]) + 1e-300)
+    # the default is the one-CTA role-split kernel up to N_E = 576 and the cluster kernel above (4 selects the cluster kernel at
+    # any N_E > 224): same zeros as the others, values to a few ulp
+    if N_E > 576:
+        assert np.array_equal(d[0], e[0], equal_nan=True) and np.array_equal(d[1], e[1], equal_nan=True) and np.array_equal(d[2], e[2])
+    for x in (d, e):
+        assert np.array_equal(x[0] == 0, c[0] == 0) and np.array_equal(np.isnan(x[0]), np.isnan(c[0])) and np.array_equal(x[2], c[2])
+        assert np.all(np.abs(x[0][ok] - c[0][ok]) <= 1e-14 * np.abs(c[0][ok]) + 1e-300)
+        assert np.all(np.abs(x[1][ok] - c[1][ok]) <= 1e-14 * np.abs(c[1][ok]) + 1e-300)
     assert np.mean(e[0][ok] == a[0][ok]) < 1.0  # it really is a different kernel (about a quarter of the values differ in the last bits)
 
 
@@ -550,7 +552,7 @@ def test_host_buffers_pinned_or_pageable_per_array_same_bits(nusi):
 
 
 def test_cluster_integrator_with_rejected_points_and_reordering(nusi):
-    """The cluster kernel (N_E >= 640) behind the same host logic as the others: rejected points (NaN fluxes, status bit, no
+    """The cluster kernel (N_E > 576) behind the same host logic as the others: rejected points (NaN fluxes, status bit, no
     effect on their neighbours), a shuffled scan that the library regroups and scatters back, a ragged batch."""
     cfg = dict(N_bins_E=700, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
     rng = np.random.default_rng(3)
