@@ -468,7 +468,7 @@ integrate_split_kernel(DeviceGrid G, const PointParams *__restrict__ params, con
   if (status_out && tid == 0) status_out[q] = status_in[p];
 }
 
-// 7 bulk warps (two CTAs per SM) up to N_bins_E = 224; 12 and 18 bulk warps (one CTA per SM: 14 / 20 warps x 96 registers) up to 384 / 576
+// 7 / 8 bulk warps (two CTAs per SM) up to N_bins_E = 224 / 256; 12 and 18 bulk warps (one CTA per SM: 14 / 20 warps x 96 registers) up to 384 / 576
 bool integrate_split_supports(int N, int NT) { return N >= 32 && N <= 576 && NT <= 704; }
 
 template <int B, int NBW, int NHW>
@@ -488,7 +488,8 @@ cudaError_t launch_integrate_split(const IntegArgs &A, int variant, cudaStream_t
   // measured against the diagonal-owned kernel on B200 (tools/gpu_wide_check.py), 4096 points: N_E = 300: 9.8 vs 16.6 ms,
   // 400: 13.8 vs 22.8, 500: 24.9 vs 60.5, 576: 28.2 vs 161.6; faster at every batch size from 8 points on
   if (A.G.N > 384) return launch_split_t<4, 18, 1>(A, s);
-  if (A.G.N > 224) return launch_split_t<4, 12, 1>(A, s);
+  if (A.G.N > 256) return launch_split_t<4, 12, 1>(A, s);
+  if (A.G.N > 224) return launch_split_t<4, 8, 1>(A, s);  // 10 warps: still two CTAs per SM
   switch (variant) {
     case 11: return launch_split_t<4, 7, 2>(A, s);  // two helper warps: 4.02 ms per 8192 points against 3.57 (the tenth warp costs more than it prepares)
     case 13: return launch_split_t<2, 7, 1>(A, s);
