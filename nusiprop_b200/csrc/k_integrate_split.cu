@@ -490,6 +490,7 @@ cudaError_t launch_integrate_split(const IntegArgs &A, int variant, cudaStream_t
   if (A.G.N > 384) return launch_split_t<4, 18, 1>(A, s);
   if (A.G.N > 256) return launch_split_t<4, 12, 1>(A, s);
   if (A.G.N > 224) return launch_split_t<4, 8, 1>(A, s);  // 10 warps: still two CTAs per SM
+  if (A.G.N <= 128 && variant == 0) return launch_split_t<4, 4, 1>(A, s);  // 6 warps, three CTAs per SM: N_E = 100: 1.71 ms per 8192 points (diagonal-owned kernel 2.89)
   switch (variant) {
     case 11: return launch_split_t<4, 7, 2>(A, s);  // two helper warps: 4.02 ms per 8192 points against 3.57 (the tenth warp costs more than it prepares)
     case 13: return launch_split_t<2, 7, 1>(A, s);
