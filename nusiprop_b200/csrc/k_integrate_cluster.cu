@@ -13,9 +13,10 @@
 //                       warp shuffle, flux-independent half from a helper slot, regeneration sum = far part published by the
 //                       diagonal's owner + the last D = 2B-1 sources kept in registers), and BROADCASTS the new weighted
 //                       flux W of the wave into the shared memory of all four CTAs (st.shared::cluster).
-//   rank 0, warps 1..2  helpers: slots (denominators, reciprocals, source term) one block of B waves ahead.
+//   ranks 0-1, warps 1..2  helpers: slots (denominators, reciprocals, source term) one block of B waves ahead, one wave each;
+//                       rank 1 writes its slots into rank 0's shared memory.
 //   all ranks, 1 warp   producer (one lane per copy): the TMA copies of this CTA's table slices, three blocks ahead.
-//   all ranks, 16 warps bulk: thread u of rank r owns diagonal d = -31 + 508 r + u: acc[s] += T[row(d)][c] W_s for every
+//   all ranks, 16 warps bulk: thread u of rank r owns diagonal d = -31 + 508 (3 - r) + u: acc[s] += T[row(d)][c] W_s for every
 //                       source more than D waves behind its cells, one block behind the critical warp; the owner of the
 //                       diagonal that is finalised in block kb+1 writes its 32 sums into rank 0's shared memory (DSMEM).
 //   every CTA streams ITS slice of each table column (the 508 rows of its diagonals) through a shared-memory ring with
@@ -32,6 +33,9 @@
 namespace nusi {
 
 #define NUSI_CL_C 4      // CTAs per cluster
+#ifndef NUSI_CL_HR
+#define NUSI_CL_HR 2     // ranks whose helper warps prepare slots (ranks >= 1 write them into rank 0's shared memory)
+#endif
 #define NUSI_CL_PF 12    // slot fields: lum, offdiag, Gam, aT, Z0, rZ0, Z1, rZ1, Z2, rZ2, dE, 1/dE
 #define NUSI_CL_RB 5     // ring depth in blocks of B columns (block kb-1 .. kb+3)
 #define NUSI_CL_PAD 16   // doubles in front of the near ring: the critical warp reads up to D rows below row 0 of a column
@@ -224,7 +228,7 @@ __device__ __forceinline__ void cl_help_load(const ClCtx &C, int kb, int hw, int
   }
 }
 template <int B, int NHW>
-__device__ __forceinline__ void cl_help_block(double *ssm, const ClCtx &C, int kb, int hw, int lane, const ClHelpIn (&hs)[(B + NHW - 1) / NHW]) {
+__device__ __forceinline__ void cl_help_block(double *ssm, const ClCtx &C, int kb, int hw, int lane, unsigned pre0, const ClHelpIn (&hs)[(B + NHW - 1) / NHW]) {
   constexpr int RH = (B + NHW - 1) / NHW, PF = NUSI_CL_PF, D = 2 * B - 1;
   const int sl = lane, zi = max(C.S - 1 - C.s0 - sl, 0), N = C.N, NT = C.NT;
   if (hw == 0 && lane < B) {  // where row c of the wave's column sits in the near ring
@@ -277,10 +281,10 @@ __device__ __forceinline__ void cl_help_block(double *ssm, const ClCtx &C, int k
     const int r = hw + q * NHW;
     if (r < B) {
       const double offdiag = fabs(aT[q]) * rdE[q] * fmax(fabs(rZ[q][0]), fmax(fabs(rZ[q][1]), fabs(rZ[q][2]))) * 1.00001;
-      double *o = ssm + C.pre + (((kb & 1) * B + r) * PF) * 32 + sl;
-      o[0 * 32] = cz * hs[q].src; o[1 * 32] = offdiag; o[2 * 32] = Gam[q]; o[3 * 32] = aT[q];
-      o[4 * 32] = Z[q][0]; o[5 * 32] = rZ[q][0]; o[6 * 32] = Z[q][1]; o[7 * 32] = rZ[q][1]; o[8 * 32] = Z[q][2]; o[9 * 32] = rZ[q][2];
-      o[10 * 32] = dEb[q]; o[11 * 32] = rdE[q];
+      const unsigned o = pre0 + (unsigned)((((kb & 1) * B + r) * PF) * 32 + sl) * 8u;  // rank 0's slot (this CTA's own when rank == 0)
+      const double fld[PF] = {cz * hs[q].src, offdiag, Gam[q], aT[q], Z[q][0], rZ[q][0], Z[q][1], rZ[q][1], Z[q][2], rZ[q][2], dEb[q], rdE[q]};
+#pragma unroll
+      for (int f = 0; f < PF; ++f) cl_st_f64(o + (unsigned)(f * 32) * 8u, fld[f]);
     }
   }
 }
@@ -354,21 +358,22 @@ static __device__ __noinline__ void cl_producer(double *ssm) {
 
 template <int B, int NHW>
 static __device__ __noinline__ void cl_helper(double *ssm) {
-  constexpr int RH = (B + NHW - 1) / NHW;
+  constexpr int NHT = NHW * NUSI_CL_HR, RH = (B + NHT - 1) / NHT;  // helper warps of the whole cluster; waves per helper and block
   const ClCtx &C = *reinterpret_cast<const ClCtx *>(ssm);
-  const int lane = threadIdx.x & 31, hw = (threadIdx.x >> 5) - 1, n_blocks = C.n_blocks;
-  const bool work = (C.rank == 0) && !(C.dbg & 4);
+  const int lane = threadIdx.x & 31, hw = C.rank * NHW + (int)(threadIdx.x >> 5) - 1, n_blocks = C.n_blocks;
+  const bool work = (C.rank < NUSI_CL_HR) && !(C.dbg & 4);
+  const unsigned pre0 = cl_mapa((unsigned)__cvta_generic_to_shared(ssm + C.pre), 0u);
   ClHelpIn hs[RH], hsn[RH];
   if (work) {
-    cl_help_load<B, NHW>(C, 1, hw, lane, hs);
-    cl_help_load<B, NHW>(C, 2, hw, lane, hsn);
+    cl_help_load<B, NHT>(C, 1, hw, lane, hs);
+    cl_help_load<B, NHT>(C, 2, hw, lane, hsn);
   }
   for (int kb = 0; kb < n_blocks; ++kb) {
     if (work) {
-      if (kb + 1 < n_blocks) cl_help_block<B, NHW>(ssm, C, kb + 1, hw, lane, hs);
+      if (kb + 1 < n_blocks) cl_help_block<B, NHT>(ssm, C, kb + 1, hw, lane, pre0, hs);
 #pragma unroll
       for (int q = 0; q < RH; ++q) hs[q] = hsn[q];
-      cl_help_load<B, NHW>(C, kb + 3, hw, lane, hsn);  // clamped indices: harmless beyond the last block
+      cl_help_load<B, NHT>(C, kb + 3, hw, lane, hsn);  // clamped indices: harmless beyond the last block
     }
     __syncwarp();
     cl_sync();
@@ -384,7 +389,10 @@ static __device__ __noinline__ void cl_bulk(double *ssm) {
 #pragma unroll
   for (int j = 0; j < 32; ++j) acc[j] = 0.0;
   const int N = C.N, u = (int)threadIdx.x - (2 + NHW) * 32;
-  const int d = -31 + C.rank * C.DPC + u;  // this thread's diagonal: cells (sl, b = d + sl)
+  // this thread's diagonal: cells (sl, b = d + sl).  Rank 0 -- the critical warp's CTA -- owns the HIGHEST diagonals: they are
+  // finalised in the first quarter of a band and receive no update afterwards, so for three quarters of the band the chain
+  // shares its SM with nobody; the long-lived low diagonals live on rank 3.
+  const int d = -31 + (NUSI_CL_C - 1 - C.rank) * C.DPC + u;
   const bool owner = (u < C.DPC) && (d <= N - 1);
   const int n_blocks = C.n_blocks, n_waves = C.n_waves, cnt = C.cnt;
   const int wd = N - 1 - d;                // the wave in which the diagonal's cells are finalised
@@ -499,7 +507,7 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
     const int n_waves = cnt - 1 + N, n_blocks = (n_waves + B - 1) / B;
     if (tid == 0) {
       C.s0 = s0; C.cnt = cnt; C.n_waves = n_waves; C.n_blocks = n_blocks; C.rowoff = S - 1 - s0; C.phase0 = ring_phase;
-      C.a0 = S - 1 - s0 - 31 + rank * DPC;
+      C.a0 = S - 1 - s0 - 31 + (NUSI_CL_C - 1 - rank) * DPC;
     }
     for (int i = tid; i < 2 * B * 32; i += NTHR) ssm[L.ash + i] = 0.0;
     __syncthreads();
@@ -507,10 +515,11 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
       const ClIssue P = cl_issue_fields(C);
       for (int kb = 0; kb < 3 && kb < n_blocks && !(dbg & 8); ++kb) cl_issue_block<B>(P, kb, tid & 31);
     }
-    if (rank == 0 && warp >= 1 && warp <= NHW) {
-      ClHelpIn hs0[(B + NHW - 1) / NHW];
-      cl_help_load<B, NHW>(C, 0, warp - 1, tid & 31, hs0);
-      cl_help_block<B, NHW>(ssm, C, 0, warp - 1, tid & 31, hs0);
+    if (rank < NUSI_CL_HR && warp >= 1 && warp <= NHW) {
+      constexpr int NHT = NHW * NUSI_CL_HR;
+      ClHelpIn hs0[(B + NHT - 1) / NHT];
+      cl_help_load<B, NHT>(C, 0, rank * NHW + warp - 1, tid & 31, hs0);
+      cl_help_block<B, NHT>(ssm, C, 0, rank * NHW + warp - 1, tid & 31, cl_mapa((unsigned)__cvta_generic_to_shared(ssm + L.pre), 0u), hs0);
     }
     __syncthreads();
     cl_sync();
