@@ -16,7 +16,8 @@
 //   ranks 0-1, warps 1..2  helpers: slots (denominators, reciprocals, source term) one block of B waves ahead, one wave each;
 //                       rank 1 writes its slots into rank 0's shared memory.
 //   all ranks, 1 warp   producer (one lane per copy): the TMA copies of this CTA's table slices, three blocks ahead.
-//   all ranks, 16 warps bulk: thread u of rank r owns diagonal d = -31 + 508 (3 - r) + u: acc[s] += T[row(d)][c] W_s for every
+//   all ranks, 16 warps bulk: a thread of rank r owns two neighbouring diagonals out of -31 + 508 (3 - r) + [0, 508) and half of the
+//                       band's z-steps: acc[s] += T[row(d)][c] W_s for every
 //                       source more than D waves behind its cells, one block behind the critical warp; the owner of the
 //                       diagonal that is finalised in block kb+1 writes its 32 sums into rank 0's shared memory (DSMEM).
 //   every CTA streams ITS slice of each table column (the 508 rows of its diagonals) through a shared-memory ring with
@@ -381,64 +382,81 @@ static __device__ __noinline__ void cl_helper(double *ssm) {
 }
 
 // ================= bulk warps (every rank): sources of block kb-1, publish the diagonal of block kb+1 =================
-template <int B, int NHW>
+// Thread u owns TWO neighbouring diagonals and HALF of the band's z-steps (the lower half of the bulk warps z-steps 0..15, the
+// upper half 16..31): 2 x 16 running sums, as many registers as one diagonal x 32 z-steps, but every broadcast load of a pair
+// of weighted fluxes feeds four FMAs instead of two (the update is bound by the shared-memory loads it has to wait for).
+template <int B, int NBW, int NHW>
 static __device__ __noinline__ void cl_bulk(double *ssm) {
-  constexpr int D = 2 * B - 1;
+  constexpr int D = 2 * B - 1, HALF = NBW * 16;  // HALF threads per z-half, each with two diagonals: 32 NBW diagonals per CTA
   const ClCtx &C = *reinterpret_cast<const ClCtx *>(ssm);
-  double acc[32];
+  double a0[16], a1[16];
 #pragma unroll
-  for (int j = 0; j < 32; ++j) acc[j] = 0.0;
+  for (int j = 0; j < 16; ++j) a0[j] = a1[j] = 0.0;
   const int N = C.N, u = (int)threadIdx.x - (2 + NHW) * 32;
-  // this thread's diagonal: cells (sl, b = d + sl).  Rank 0 -- the critical warp's CTA -- owns the HIGHEST diagonals: they are
-  // finalised in the first quarter of a band and receive no update afterwards, so for three quarters of the band the chain
-  // shares its SM with nobody; the long-lived low diagonals live on rank 3.
-  const int d = -31 + (NUSI_CL_C - 1 - C.rank) * C.DPC + u;
-  const bool owner = (u < C.DPC) && (d <= N - 1);
+  const int zh = (u >= HALF) ? 1 : 0, dp = u - zh * HALF;
+  // Rank 0 -- the critical warp's CTA -- owns the HIGHEST diagonals: they are finalised in the first quarter of a band and
+  // receive no update afterwards, so for three quarters of the band the chain shares its SM with nobody; the long-lived
+  // low diagonals live on rank 3.
+  const int d0 = -31 + (NUSI_CL_C - 1 - C.rank) * C.DPC + 2 * dp;  // cells (sl, b = d + sl); the second diagonal is d0 + 1
+  const bool own0 = (2 * dp < C.DPC) && (d0 <= N - 1), own1 = (2 * dp + 1 < C.DPC) && (d0 + 1 <= N - 1);
   const int n_blocks = C.n_blocks, n_waves = C.n_waves, cnt = C.cnt;
-  const int wd = N - 1 - d;                // the wave in which the diagonal's cells are finalised
-  const int row = C.a0 + u;                // its table row in this band
+  const int wd0 = N - 1 - d0, wd1 = wd0 - 1;  // the waves in which the diagonals' cells are finalised
+  const int row0 = C.a0 + 2 * dp;             // table row of d0 in this band (d0 + 1: the next row)
   const int as = max(C.a0, 0);
   const unsigned mbar0 = C.mbar0, phase0 = C.phase0, tpar = C.tpar;
-  const unsigned ash0 = cl_mapa(C.ash_s, 0u);  // rank 0's hand-over slots
+  const unsigned ash0 = cl_mapa(C.ash_s, 0u) + (unsigned)(16 * zh) * 8u;  // rank 0's hand-over slots, this thread's z-half
   for (int kb = 0; kb < n_blocks; ++kb) {
-    if (kb >= 1 && owner && !(C.dbg & 1)) {
+    if (kb >= 1 && (own0 || own1) && !(C.dbg & 1)) {
       const int kbs = kb - 1;
       mbar_wait(mbar0 + 8u * (kbs % NUSI_CL_RB), cl_parity(phase0, kbs));
 #pragma unroll
       for (int r = 0; r < B; ++r) {
         const int w_rel = kbs * B + r;
-        if (w_rel < n_waves && wd - w_rel > D && row >= 0) {
+        const bool act0 = own0 && w_rel < n_waves && wd0 - w_rel > D && row0 >= 0;
+        const bool act1 = own1 && w_rel < n_waves && wd1 - w_rel > D && row0 + 1 >= 0;
+        const int hi = min(w_rel, cnt - 1) - 16 * zh;  // last z-step of this half that has started
+        if ((act0 || act1) && hi >= 0) {
           const int c = C.NT - 1 - (C.s0 + w_rel);
-          const double tv = ssm[C.ring + ((kbs % NUSI_CL_RB) * B + r) * C.SLOT + cl_mis(tpar, c, as) + (row - as)];
-          const double *Wp = ssm + C.wsh + ((kbs & 1) * B + r) * 32;
-          const int hi = min(w_rel, cnt - 1);  // z-steps that have started
+          const double *col = ssm + C.ring + ((kbs % NUSI_CL_RB) * B + r) * C.SLOT + cl_mis(tpar, c, as) - as;
+          const double t0 = act0 ? col[row0] : 0.0, t1 = act1 ? col[row0 + 1] : 0.0;  // an inactive diagonal adds 0 x W
+          const double *Wp = ssm + C.wsh + ((kbs & 1) * B + r) * 32 + 16 * zh;
           const unsigned wp_s = (unsigned)__cvta_generic_to_shared(Wp);
-          if (hi == 31) {
+          if (hi >= 15) {
 #pragma unroll
-            for (int s8 = 0; s8 < 32; s8 += 8) {
-              double2 w2[4];
-#pragma unroll
-              for (int q = 0; q < 4; ++q) w2[q] = lds_f64x2(wp_s + (unsigned)(s8 + 2 * q) * 8u);
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                acc[s8 + 2 * q] = fma(tv, w2[q].x, acc[s8 + 2 * q]);
-                acc[s8 + 2 * q + 1] = fma(tv, w2[q].y, acc[s8 + 2 * q + 1]);
-              }
+            for (int s4 = 0; s4 < 16; s4 += 4) {
+              const double2 wa = lds_f64x2(wp_s + (unsigned)s4 * 8u), wb = lds_f64x2(wp_s + (unsigned)(s4 + 2) * 8u);
+              a0[s4] = fma(t0, wa.x, a0[s4]);
+              a1[s4] = fma(t1, wa.x, a1[s4]);
+              a0[s4 + 1] = fma(t0, wa.y, a0[s4 + 1]);
+              a1[s4 + 1] = fma(t1, wa.y, a1[s4 + 1]);
+              a0[s4 + 2] = fma(t0, wb.x, a0[s4 + 2]);
+              a1[s4 + 2] = fma(t1, wb.x, a1[s4 + 2]);
+              a0[s4 + 3] = fma(t0, wb.y, a0[s4 + 3]);
+              a1[s4 + 3] = fma(t1, wb.y, a1[s4 + 3]);
             }
           } else {
 #pragma unroll
-            for (int sl = 0; sl < 32; ++sl)
-              if (sl <= hi) acc[sl] = fma(tv, Wp[sl], acc[sl]);
+            for (int sl = 0; sl < 16; ++sl)
+              if (sl <= hi) {
+                const double w = Wp[sl];
+                a0[sl] = fma(t0, w, a0[sl]);
+                a1[sl] = fma(t1, w, a1[sl]);
+              }
           }
         }
       }
     }
-    if (owner) {  // hand the sums of the diagonal that is finalised in block kb+1 to the critical warp
+    {  // hand the sums of a diagonal that is finalised in block kb+1 to the critical warp (this thread's 16 z-steps of it)
       const int lo_b = (kb + 1) * B, hi_b = (kb + 2) * B;
-      if (wd >= lo_b && wd < hi_b && wd < n_waves) {
-        const unsigned o = ash0 + (unsigned)((((kb + 1) & 1) * B + (wd - lo_b)) * 32) * 8u;
+      if (own0 && wd0 >= lo_b && wd0 < hi_b && wd0 < n_waves) {
+        const unsigned o = ash0 + (unsigned)((((kb + 1) & 1) * B + (wd0 - lo_b)) * 32) * 8u;
 #pragma unroll
-        for (int sl = 0; sl < 32; sl += 2) cl_st_f64x2(o + (unsigned)sl * 8u, acc[sl], acc[sl + 1]);
+        for (int sl = 0; sl < 16; sl += 2) cl_st_f64x2(o + (unsigned)sl * 8u, a0[sl], a0[sl + 1]);
+      }
+      if (own1 && wd1 >= lo_b && wd1 < hi_b && wd1 < n_waves) {
+        const unsigned o = ash0 + (unsigned)((((kb + 1) & 1) * B + (wd1 - lo_b)) * 32) * 8u;
+#pragma unroll
+        for (int sl = 0; sl < 16; sl += 2) cl_st_f64x2(o + (unsigned)sl * 8u, a1[sl], a1[sl + 1]);
       }
     }
     __syncwarp();
@@ -459,7 +477,7 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
   const int rank = (int)cl_rank();
   const int p = blockIdx.x / NUSI_CL_C;
   const int N = G.N, NT = G.NT, S = G.Nz - 1;
-  const int DPC = (N + 31 + NUSI_CL_C - 1) / NUSI_CL_C;
+  const int DPC = ((N + 31 + NUSI_CL_C - 1) / NUSI_CL_C + 1) & ~1;  // diagonals per CTA (even: a bulk thread owns two)
   const bool dead = !(params[p].mphi > 0);
   const ClLayout L = cl_layout(N, S, B, DPC);
   ClCtx &C = *reinterpret_cast<ClCtx *>(ssm);
@@ -534,7 +552,7 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
     } else if (warp == 1 + NHW) {
       cl_producer<B>(ssm);
     } else {
-      cl_bulk<B, NHW>(ssm);
+      cl_bulk<B, NBW, NHW>(ssm);
     }
 #pragma unroll
     for (int i = 0; i < NUSI_CL_RB; ++i)
@@ -558,7 +576,7 @@ bool integrate_cluster_supports(int N, int NT) { return N > 224 && N + 31 <= NUS
 template <int B, int NBW, int NHW>
 static cudaError_t launch_cluster_t(const IntegArgs &A, cudaStream_t s, int dbg) {
   const DeviceGrid &G = A.G;
-  const int DPC = (G.N + 31 + NUSI_CL_C - 1) / NUSI_CL_C;
+  const int DPC = ((G.N + 31 + NUSI_CL_C - 1) / NUSI_CL_C + 1) & ~1;
   const ClLayout L = cl_layout(G.N, G.Nz - 1, B, DPC);
   const size_t sh = (size_t)L.total * sizeof(double);
   cudaError_t e = cudaFuncSetAttribute(integrate_cluster_kernel<B, NBW, NHW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
