@@ -617,8 +617,15 @@ static int launch_integrate_stage(nusi_ctx *c, const IntegArgs &A, cudaStream_t 
     e = launch_integrate_split(A, c->opt.fine_variant, s);
   // beyond the one-CTA role-split kernel's reach (N_bins_E > 576: 20 warps x 96 registers fill the SM): one point over a 4-CTA
   // cluster.  The choice depends on the binning alone, so that a point's bits do not depend on the size of its batch.
-  else if ((c->opt.integrator == 0 || c->opt.integrator == 4) && integrate_cluster_supports(c->G.N, c->G.NT))
+  else if ((c->opt.integrator == 0 || c->opt.integrator == 4) && integrate_cluster_supports(c->G.N, c->G.NT)) {
     e = launch_integrate_cluster(A, c->opt.fine_variant, s);
+    // a device (or partition) that cannot co-schedule a 4-CTA cluster with this much shared memory: the one-CTA kernel
+    if ((e == cudaErrorLaunchOutOfResources || e == cudaErrorInvalidConfiguration || e == cudaErrorInvalidClusterSize || e == cudaErrorInvalidValue) &&
+        integrate_diag_supports(c->G.N, c->G.NT)) {
+      cudaGetLastError();
+      e = launch_integrate_diag(A, c->opt.fine_variant, s);
+    }
+  }
   else
     e = launch_integrate_diag(A, c->opt.fine_variant, s);
   if (e == cudaErrorInvalidValue) return fail(NUSI_E_INVALID, "binning not supported by the selected integrator");
