@@ -81,7 +81,7 @@ typedef struct nusi_opts {
    *      kernels and tuning variants that produce the same numbers; tests and tools set them here, nothing in the
    *      library reads the environment. */
   int integrator;        /* 0 = default: role-split wavefront kernel, one CTA per point (32 <= N_bins_E <= 576) or one point over a
-                                thread-block cluster of 4 CTAs (577 <= N_bins_E <= 2017); diagonal-owned wavefront kernel otherwise;
+                                thread-block cluster of 2 / 4 CTAs (577 <= N_bins_E <= 993 / 2017); diagonal-owned wavefront kernel otherwise;
                             1 = bin-owned wavefront kernel (cross-check);
                             2 = serial, reference-shaped bin-by-bin kernel with true divisions (cross-check, N_bins_E <= 256);
                             3 = diagonal-owned wavefront kernel at every binning;

@@ -1,6 +1,6 @@
 // k_integrate_cluster.cu -- the implicit z-stepping integrator (reference nuSIprop.hpp:255-336) for FINE binnings
 // (N_bins_E > 224, BASELINE configs[3]: N_E = 2000): the role-split wavefront of k_integrate_split.cu with ONE POINT
-// SPREAD OVER A THREAD-BLOCK CLUSTER of 4 CTAs (4 SMs).   (sm_100a, FP64 pipe; -fmad=false: contraction only where fma() is written)
+// SPREAD OVER A THREAD-BLOCK CLUSTER of 4 CTAs (4 SMs; 2 CTAs up to N_bins_E = 993).   (sm_100a, FP64 pipe; -fmad=false: contraction only where fma() is written)
 //
 // Why a cluster: the wavefront needs one running sum per (table diagonal, z-step of the band).  At N_E = 2000 that is
 // 2031 diagonals x 32 z-steps x 8 B = 520 KB -- more than one SM's register file, which is why the one-CTA-per-point
@@ -33,7 +33,7 @@
 
 namespace nusi {
 
-#define NUSI_CL_C 4      // CTAs per cluster
+#define NUSI_CL_C 4      // most CTAs per cluster (the kernel is instantiated for clusters of 2 and 4)
 #ifndef NUSI_CL_HR
 #define NUSI_CL_HR 2     // ranks whose helper warps prepare slots (ranks >= 1 write them into rank 0's shared memory)
 #endif
@@ -64,7 +64,7 @@ __device__ __forceinline__ void cl_sync() {
 }
 
 struct ClCtx {  // at the start of dynamic shared memory of every CTA, filled by its thread 0
-  int N, NT, S, NP, SLOT, DPC, rank, dbg;
+  int N, NT, S, NP, SLOT, DPC, rank, dbg, csize;  // csize: CTAs of the cluster
   int s0, cnt, n_waves, n_blocks, rowoff, a0;  // a0: table row of this CTA's first diagonal in this band (may be negative)
   int ring, near, wsh, ash, pre, sdE, sRdE, sCz, sNd, fband, tcoff, fb;  // offsets in doubles
   unsigned mbar0, ring0, near0, phase0, tpar, wsh_s, ash_s;              // shared::cta byte addresses
@@ -108,9 +108,9 @@ __device__ __forceinline__ unsigned cl_parity(unsigned phase0, int kb) {  // par
 }
 
 // One wave of the critical warp (split_wave of k_integrate_split.cu; W goes to all CTAs of the cluster).
-template <int D, bool ALL>
+template <int D, bool ALL, int CC>
 __device__ __forceinline__ void cl_wave(bool act, int sl, int cnt, int bb, int NP, double U0, double U1, double U2, double czl, double ndl,
-                                        const double *__restrict__ slot, const double *__restrict__ ash, const unsigned (&wdst)[NUSI_CL_C],
+                                        const double *__restrict__ slot, const double *__restrict__ ash, const unsigned (&wdst)[CC],
                                         unsigned woff, const double *__restrict__ tc, double *__restrict__ fband, double *__restrict__ fb,
                                         double (&ip)[D], double &o0, double &o1, double &o2) {
   const double u0 = __shfl_up_sync(0xffffffffu, o0, 1), u1 = __shfl_up_sync(0xffffffffu, o1, 1), u2 = __shfl_up_sync(0xffffffffu, o2, 1);
@@ -137,7 +137,7 @@ __device__ __forceinline__ void cl_wave(bool act, int sl, int cnt, int bb, int N
   }
   const double Wp = (ALL || act) ? W : 0.0;
 #pragma unroll
-  for (int r = 0; r < NUSI_CL_C; ++r) cl_st_f64(wdst[r] + woff, Wp);
+  for (int r = 0; r < CC; ++r) cl_st_f64(wdst[r] + woff, Wp);
   if (ALL) {
     o0 = v0;
     o1 = v1;
@@ -163,7 +163,7 @@ __device__ __forceinline__ void cl_wave(bool act, int sl, int cnt, int bb, int N
 }
 
 // ================= critical warp (rank 0) =================
-template <int B>
+template <int B, int CC>
 static __device__ __noinline__ void cl_critical(double *ssm) {
   constexpr int D = 2 * B - 1, PF = NUSI_CL_PF;
   const ClCtx &C = *reinterpret_cast<const ClCtx *>(ssm);
@@ -176,9 +176,9 @@ static __device__ __noinline__ void cl_critical(double *ssm) {
   double o0 = 0.0, o1 = 0.0, o2 = 0.0;
   const double czl = (sl < cnt) ? ssm[C.sCz + C.S - 1 - C.s0 - sl] : 0.0, ndl = (sl < cnt) ? ssm[C.sNd + C.S - 1 - C.s0 - sl] : 0.0;
   const unsigned mbar0 = C.mbar0, phase0 = C.phase0;
-  unsigned wdst[NUSI_CL_C];
+  unsigned wdst[CC];
 #pragma unroll
-  for (int r = 0; r < NUSI_CL_C; ++r) wdst[r] = cl_mapa(C.wsh_s, (unsigned)r) + (unsigned)sl * 8u;
+  for (int r = 0; r < CC; ++r) wdst[r] = cl_mapa(C.wsh_s, (unsigned)r) + (unsigned)sl * 8u;
   for (int kb = 0; kb < n_blocks; ++kb) {
     if (!(C.dbg & 8)) mbar_wait(mbar0 + 8u * (kb % NUSI_CL_RB), cl_parity(phase0, kb));
     const double *slotB = ssm + C.pre + ((kb & 1) * B * PF) * 32 + sl;
@@ -191,18 +191,18 @@ static __device__ __noinline__ void cl_critical(double *ssm) {
 #pragma unroll
       for (int r = 0; r < B; ++r)
 #pragma unroll
-        for (int q = 0; q < NUSI_CL_C; ++q) cl_st_f64(wdst[q] + woffB + (unsigned)(r * 32) * 8u, 1e-3);
+        for (int q = 0; q < CC; ++q) cl_st_f64(wdst[q] + woffB + (unsigned)(r * 32) * 8u, 1e-3);
     } else if (all) {
 #pragma unroll
       for (int r = 0; r < B; ++r)
-        cl_wave<D, true>(true, sl, cnt, N - 1 - (k0 + r), NP, U0, U1, U2, czl, ndl, slotB + r * PF * 32, ashB + r * 32, wdst, woffB + (unsigned)(r * 32) * 8u,
+        cl_wave<D, true, CC>(true, sl, cnt, N - 1 - (k0 + r), NP, U0, U1, U2, czl, ndl, slotB + r * PF * 32, ashB + r * 32, wdst, woffB + (unsigned)(r * 32) * 8u,
                          ssm + tco[r], fband, fb, ip, o0, o1, o2);
     } else {
 #pragma unroll
       for (int r = 0; r < B; ++r) {
         const int k = k0 + r;
         const bool act = (sl < cnt) && (k >= 0) && (k <= N - 1);
-        cl_wave<D, false>(act, sl, cnt, act ? N - 1 - k : 0, NP, U0, U1, U2, czl, ndl, slotB + r * PF * 32, ashB + r * 32, wdst, woffB + (unsigned)(r * 32) * 8u,
+        cl_wave<D, false, CC>(act, sl, cnt, act ? N - 1 - k : 0, NP, U0, U1, U2, czl, ndl, slotB + r * PF * 32, ashB + r * 32, wdst, woffB + (unsigned)(r * 32) * 8u,
                           ssm + tco[r], fband, fb, ip, o0, o1, o2);
       }
     }
@@ -397,7 +397,7 @@ static __device__ __noinline__ void cl_bulk(double *ssm) {
   // Rank 0 -- the critical warp's CTA -- owns the HIGHEST diagonals: they are finalised in the first quarter of a band and
   // receive no update afterwards, so for three quarters of the band the chain shares its SM with nobody; the long-lived
   // low diagonals live on rank 3.
-  const int d0 = -31 + (NUSI_CL_C - 1 - C.rank) * C.DPC + 2 * dp;  // cells (sl, b = d + sl); the second diagonal is d0 + 1
+  const int d0 = -31 + (C.csize - 1 - C.rank) * C.DPC + 2 * dp;  // cells (sl, b = d + sl); the second diagonal is d0 + 1
   const bool own0 = (2 * dp < C.DPC) && (d0 <= N - 1), own1 = (2 * dp + 1 < C.DPC) && (d0 + 1 <= N - 1);
   const int n_blocks = C.n_blocks, n_waves = C.n_waves, cnt = C.cnt;
   const int wd0 = N - 1 - d0, wd1 = wd0 - 1;  // the waves in which the diagonals' cells are finalised
@@ -465,8 +465,8 @@ static __device__ __noinline__ void cl_bulk(double *ssm) {
 }
 
 // B waves per block; NBW bulk warps per CTA (N_bins_E + 31 <= 4 x 32 NBW); NHW helper warps
-template <int B, int NBW, int NHW>
-__global__ void __cluster_dims__(NUSI_CL_C, 1, 1) __launch_bounds__((2 + NHW + NBW) * 32, (NBW <= 4 ? 2 : 1))
+template <int B, int NBW, int NHW, int CC>
+__global__ void __launch_bounds__((2 + NHW + NBW) * 32, (NBW <= 4 ? 2 : 1))
 integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, const double *__restrict__ rows,
                          const double *__restrict__ tri, size_t tstride, double *__restrict__ flux_mass,
                          double *__restrict__ flux_fla, const int *__restrict__ out_index, const int *__restrict__ status_in,
@@ -475,9 +475,9 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
   extern __shared__ __align__(16) double ssm[];
   const int tid = threadIdx.x, warp = tid >> 5;
   const int rank = (int)cl_rank();
-  const int p = blockIdx.x / NUSI_CL_C;
+  const int p = blockIdx.x / CC;
   const int N = G.N, NT = G.NT, S = G.Nz - 1;
-  const int DPC = ((N + 31 + NUSI_CL_C - 1) / NUSI_CL_C + 1) & ~1;  // diagonals per CTA (even: a bulk thread owns two)
+  const int DPC = ((N + 31 + CC - 1) / CC + 1) & ~1;  // diagonals per CTA (even: a bulk thread owns two)
   const bool dead = !(params[p].mphi > 0);
   const ClLayout L = cl_layout(N, S, B, DPC);
   ClCtx &C = *reinterpret_cast<ClCtx *>(ssm);
@@ -500,7 +500,7 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
     for (int i = 0; i < NUSI_CL_RB; ++i) mbar_init(mbar0 + 8u * i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     const PointParams P = params[p];
-    C.N = N; C.NT = NT; C.S = S; C.NP = NP; C.SLOT = L.SLOT; C.DPC = DPC; C.rank = rank; C.dbg = dbg;
+    C.N = N; C.NT = NT; C.S = S; C.NP = NP; C.SLOT = L.SLOT; C.DPC = DPC; C.rank = rank; C.dbg = dbg; C.csize = CC;
     C.ring = L.ring; C.near = L.near; C.wsh = L.wsh; C.ash = L.ash; C.pre = L.pre; C.sdE = L.sdE; C.sRdE = L.sRdE;
     C.sCz = L.sCz; C.sNd = L.sNd; C.fband = L.fband; C.tcoff = L.tcoff; C.fb = L.fb;
     C.mbar0 = mbar0;
@@ -525,7 +525,7 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
     const int n_waves = cnt - 1 + N, n_blocks = (n_waves + B - 1) / B;
     if (tid == 0) {
       C.s0 = s0; C.cnt = cnt; C.n_waves = n_waves; C.n_blocks = n_blocks; C.rowoff = S - 1 - s0; C.phase0 = ring_phase;
-      C.a0 = S - 1 - s0 - 31 + (NUSI_CL_C - 1 - rank) * DPC;
+      C.a0 = S - 1 - s0 - 31 + (CC - 1 - rank) * DPC;
     }
     for (int i = tid; i < 2 * B * 32; i += NTHR) ssm[L.ash + i] = 0.0;
     __syncthreads();
@@ -543,7 +543,7 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
     cl_sync();
     if (warp == 0) {
       if (rank == 0) {
-        cl_critical<B>(ssm);
+        cl_critical<B, CC>(ssm);
       } else {
         for (int kb = 0; kb < n_blocks; ++kb) cl_sync();
       }
@@ -573,26 +573,46 @@ integrate_cluster_kernel(DeviceGrid G, const PointParams *__restrict__ params, c
 
 bool integrate_cluster_supports(int N, int NT) { return N > 224 && N + 31 <= NUSI_CL_C * 32 * 16 && NT > 0; }
 
-template <int B, int NBW, int NHW>
+template <int B, int NBW, int NHW, int CC>
 static cudaError_t launch_cluster_t(const IntegArgs &A, cudaStream_t s, int dbg) {
   const DeviceGrid &G = A.G;
-  const int DPC = ((G.N + 31 + NUSI_CL_C - 1) / NUSI_CL_C + 1) & ~1;
+  const int DPC = ((G.N + 31 + CC - 1) / CC + 1) & ~1;
   const ClLayout L = cl_layout(G.N, G.Nz - 1, B, DPC);
   const size_t sh = (size_t)L.total * sizeof(double);
-  cudaError_t e = cudaFuncSetAttribute(integrate_cluster_kernel<B, NBW, NHW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
+  auto kern = integrate_cluster_kernel<B, NBW, NHW, CC>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh);
   if (e != cudaSuccess) return e;
-  integrate_cluster_kernel<B, NBW, NHW><<<A.cnt * NUSI_CL_C, (2 + NHW + NBW) * 32, sh, s>>>(G, A.params, A.rows, A.tri, A.tstride, A.flux_mass, A.flux_fla,
-                                                                                         A.out_index, A.status_in, A.status_out, dbg);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)A.cnt * CC);
+  cfg.blockDim = dim3((2 + NHW + NBW) * 32);
+  cfg.dynamicSmemBytes = sh;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = CC;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, G, A.params, A.rows, A.tri, A.tstride, A.flux_mass, A.flux_fla, A.out_index, A.status_in, A.status_out, dbg);
 }
 
-// variant: 0 = the product configuration; 20 + bits = timing experiments with wrong results (1 no bulk update, 2 no critical chain, 4 no helper work, 8 no table copies)
+// A band of 32 z-steps needs N_bins_E + 31 running sums per z-step: up to 1024 diagonals over a cluster of 2 CTAs (twice as
+// many points in flight), up to 2048 over a cluster of 4.
+// variant: 0 = the product configuration; 12 = clusters of 4 at every binning; 20 + bits = timing experiments with wrong results
+// (1 no bulk update, 2 no critical chain, 4 no helper work, 8 no table copies)
 cudaError_t launch_integrate_cluster(const IntegArgs &A, int variant, cudaStream_t s) {
   const int need = A.G.N + 31;  // diagonals of a band
   const int dbg = variant >= 20 ? variant - 20 : 0;
-  if (need <= NUSI_CL_C * 32 * 4) return launch_cluster_t<4, 4, 2>(A, s, dbg);
-  if (need <= NUSI_CL_C * 32 * 8) return launch_cluster_t<4, 8, 2>(A, s, dbg);
-  if (need <= NUSI_CL_C * 32 * 16) return variant == 11 ? launch_cluster_t<4, 16, 1>(A, s, 0) : launch_cluster_t<4, 16, 2>(A, s, dbg);
+  if (variant != 12) {
+    if (need <= 2 * 32 * 4) return launch_cluster_t<4, 4, 2, 2>(A, s, dbg);
+    if (need <= 2 * 32 * 8) return launch_cluster_t<4, 8, 2, 2>(A, s, dbg);
+    if (need <= 2 * 32 * 16) return launch_cluster_t<4, 16, 2, 2>(A, s, dbg);
+  } else {
+    if (need <= 4 * 32 * 4) return launch_cluster_t<4, 4, 2, 4>(A, s, dbg);
+    if (need <= 4 * 32 * 8) return launch_cluster_t<4, 8, 2, 4>(A, s, dbg);
+  }
+  if (need <= 4 * 32 * 16) return variant == 11 ? launch_cluster_t<4, 16, 1, 4>(A, s, 0) : launch_cluster_t<4, 16, 2, 4>(A, s, dbg);
   return cudaErrorInvalidValue;
 }
 

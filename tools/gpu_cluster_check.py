@@ -15,19 +15,19 @@ import nusiprop_b200 as nb  # noqa: E402
 sizes = [int(a) for a in sys.argv[1:] if a.isdigit()] or [300, 500, 900, 1100, 2000]
 # batches: where the cluster kernel (4 SMs per point) beats the one-CTA-per-point kernel
 if "--batch" in sys.argv:
-    for N in (300, 400, 500, 700, 900, 1100):
+    for N in (600, 700, 800, 993):
         cfg = dict(N_bins_E=N, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
         line = "N=%d:" % N
-        for npts in (8, 32, 74, 148, 592):
+        for npts in (8, 32, 148, 592, 4096):
             mphi, g = np.repeat(10 ** np.linspace(1.5, 3.5, (npts + 7) // 8), 8)[:npts], np.tile(10 ** np.linspace(-4, -1, 8), (npts + 7) // 8)[:npts]
             t = {}
-            for integ in (3, 4):
-                ctx = nb.Context(integrator=integ, **cfg)
+            for integ, var in ((3, 0), (4, 0), (4, 12)):
+                ctx = nb.Context(integrator=integ, fine_variant=var, **cfg)
                 for _ in range(2):
                     ctx.evolve(mphi, g, 0.1)
-                    t[integ] = ctx.last_timing()["ms_integrate"]
+                    t[(integ, var)] = ctx.last_timing()["ms_integrate"]
                 ctx.close()
-            line += "  %d pts diag %.2f cluster %.2f" % (npts, t[3], t[4])
+            line += "  %d pts diag %.2f cluster %.2f (clusters of 4: %.2f)" % (npts, t[(3, 0)], t[(4, 0)], t[(4, 12)])
         print(line, flush=True)
     sys.exit(0)
 
