@@ -1,28 +1,29 @@
 // k_integrate_cluster.cu -- the implicit z-stepping integrator (reference nuSIprop.hpp:255-336) for FINE binnings
-// (N_bins_E > 224, BASELINE configs[3]: N_E = 2000): the role-split wavefront of k_integrate_split.cu with ONE POINT
-// SPREAD OVER A THREAD-BLOCK CLUSTER of 4 CTAs (4 SMs; 2 CTAs up to N_bins_E = 993).   (sm_100a, FP64 pipe; -fmad=false: contraction only where fma() is written)
+// (576 < N_bins_E <= 2017; BASELINE configs[3]: N_E = 2000): the role-split wavefront of k_integrate_split.cu with ONE POINT
+// SPREAD OVER A THREAD-BLOCK CLUSTER of 4 CTAs (4 SMs; 2 CTAs up to N_bins_E = 993).
+// (sm_100a, FP64 pipe; -fmad=false: contraction only where fma() is written)
 //
 // Why a cluster: the wavefront needs one running sum per (table diagonal, z-step of the band).  At N_E = 2000 that is
 // 2031 diagonals x 32 z-steps x 8 B = 520 KB -- more than one SM's register file, which is why the one-CTA-per-point
 // kernel (integrate_diag_kernel) has to cut the z-axis into 39 bands of 8 z-steps and walk the 2007 waves of a band 39
 // times (78 k dependent waves, 1.9 us each: 0.15 s per point).  Four SMs hold the sums of a 32-step band in registers
-// (508 diagonals per CTA, one per thread), so a point takes 10 bands = 20 k waves, and the wave-to-wave chain is carried
-// by one warp as in integrate_split_kernel instead of by two block-wide barriers per wave.
+// (508 diagonals per CTA), so a point takes 10 bands = 20 k waves, and the wave-to-wave chain is carried by one warp as
+// in integrate_split_kernel instead of by two block-wide barriers per wave.
 //
-//   rank 0, warp 0      critical warp: lane = z-step.  Finalises one cell per lane and wave (flux of the previous z-step by
-//                       warp shuffle, flux-independent half from a helper slot, regeneration sum = far part published by the
-//                       diagonal's owner + the last D = 2B-1 sources kept in registers), and BROADCASTS the new weighted
-//                       flux W of the wave into the shared memory of all four CTAs (st.shared::cluster).
-//   ranks 0-1, warps 1..2  helpers: slots (denominators, reciprocals, source term) one block of B waves ahead, one wave each;
-//                       rank 1 writes its slots into rank 0's shared memory.
-//   all ranks, 1 warp   producer (one lane per copy): the TMA copies of this CTA's table slices, three blocks ahead.
-//   all ranks, 16 warps bulk: a thread of rank r owns two neighbouring diagonals out of -31 + 508 (3 - r) + [0, 508) and half of the
-//                       band's z-steps: acc[s] += T[row(d)][c] W_s for every
-//                       source more than D waves behind its cells, one block behind the critical warp; the owner of the
-//                       diagonal that is finalised in block kb+1 writes its 32 sums into rank 0's shared memory (DSMEM).
-//   every CTA streams ITS slice of each table column (the 508 rows of its diagonals) through a shared-memory ring with
-//   TMA bulk copies (cp.async.bulk + mbarrier), three blocks ahead; rank 0 also fetches the D near-diagonal rows the
-//   critical warp needs.  One cluster barrier (barrier.cluster.arrive.release / wait.acquire) per block of B = 4 waves.
+//   rank 0, warp 0         critical warp: lane = z-step.  Finalises one cell per lane and wave (flux of the previous z-step
+//                          by warp shuffle, flux-independent half from a helper slot, regeneration sum = far part published
+//                          by the diagonal's owners + the last D = 2B-1 sources kept in registers), and BROADCASTS the new
+//                          weighted flux W of the wave into the shared memory of every CTA of the cluster (st.shared::cluster).
+//   ranks 0-1, warps 1..2  helpers: slots (denominators, reciprocals, source term) one block of B waves ahead, one wave
+//                          each; rank 1 writes its slots into rank 0's shared memory.
+//   all ranks, 1 warp      producer (one lane per copy): the TMA copies of this CTA's table slices, three blocks ahead.
+//   all ranks, 16 warps    bulk: a thread owns two neighbouring diagonals of its rank's 508 and half of the band's z-steps:
+//                          acc[s] += T[row(d)][c] W_s for every source more than D waves behind its cells, one block behind
+//                          the critical warp; the owners of the diagonal that is finalised in block kb+1 write its 32 sums
+//                          into rank 0's shared memory (DSMEM).  Rank 0 owns the highest (short-lived) diagonals.
+//   every CTA streams ITS slice of each table column (the rows of its diagonals) through a shared-memory ring with TMA
+//   bulk copies (cp.async.bulk + mbarrier), three blocks ahead; rank 0 also fetches the D near-diagonal rows the critical
+//   warp needs.  One cluster barrier (barrier.cluster.arrive.release / wait.acquire) per block of B = 4 waves.
 //
 // Summation order: as integrate_split_kernel -- a cell's regeneration sum is (far part) + (near part), each accumulated
 // in the reference's order (source bins high -> low); it differs from the strictly sequential sum by rounding only.
