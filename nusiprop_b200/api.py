@@ -106,13 +106,21 @@ class Context(object):
                                              np.atleast_1d(np.asarray(mntot, dtype=np.float64)))
         return (np.ascontiguousarray(mphi), np.ascontiguousarray(g), np.ascontiguousarray(mntot))
 
-    def evolve(self, mphi, g, mntot, want_mass=True, want_flavour=True):
-        """Host arrays in, host arrays out: (flux_mass[n,3,N], flux_fla[n,3,N], status[n])."""
+    def evolve(self, mphi, g, mntot, want_mass=True, want_flavour=True, out=None):
+        """Host arrays in, host arrays out: (flux_mass[n,3,N], flux_fla[n,3,N], status[n]).
+        out: optional (flux_mass, flux_fla, status) arrays to fill instead of new ones (C-contiguous float64 [n,3,N] and int32
+        [n]; a None entry gets a new array).  Page-locked arrays -- e.g. torch.empty(shape, dtype=torch.float64,
+        pin_memory=True).numpy() -- are written by the copy engine directly and can be reused from call to call: the fast
+        path for scans (INTEGRATION.md)."""
         mphi, g, mntot = self._points(mphi, g, mntot)
         n, N = mphi.size, self.N_bins_E
-        fm = np.empty((n, 3, N)) if want_mass else None
-        ff = np.empty((n, 3, N)) if want_flavour else None
-        st = np.zeros(n, dtype=np.int32)
+        o_fm, o_ff, o_st = out if out is not None else (None, None, None)
+        for a, shape, dt in ((o_fm, (n, 3, N), np.float64), (o_ff, (n, 3, N), np.float64), (o_st, (n,), np.int32)):
+            if a is not None and not (isinstance(a, np.ndarray) and a.shape == shape and a.dtype == dt and a.flags["C_CONTIGUOUS"] and a.flags["WRITEABLE"]):
+                raise ValueError("out arrays must be writeable C-contiguous float64 [n,3,N] / int32 [n] numpy arrays")
+        fm = (o_fm if o_fm is not None else np.empty((n, 3, N))) if want_mass else None
+        ff = (o_ff if o_ff is not None else np.empty((n, 3, N))) if want_flavour else None
+        st = o_st if o_st is not None else np.zeros(n, dtype=np.int32)
         check(self._lib.nusi_evolve_batch(self._h, n, _dp(mphi), _dp(g), _dp(mntot), _dp(fm), _dp(ff), _ip(st)), "nusi_evolve_batch")
         return fm, ff, st
 

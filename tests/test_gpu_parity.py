@@ -544,6 +544,14 @@ def test_host_buffers_pinned_or_pageable_per_array_same_bits(nusi):
             fm[:], ff[:], st[:] = -1.0, -1.0, -1
             assert ctx._lib.nusi_evolve_batch(ctx._h, n, _dp(mphi), _dp(g), _dp(mntot), _dp(fm), _dp(ff), _ip(st)) == 0
             assert np.array_equal(fm, ref[0], equal_nan=True) and np.array_equal(ff, ref[1], equal_nan=True) and np.array_equal(st, ref[2]), (host_copy, pin)
+        # the Python entry point with caller-owned (page-locked) arrays, reused
+        outs = (torch.empty((n, 3, N), dtype=torch.float64, pin_memory=True).numpy(), torch.empty((n, 3, N), dtype=torch.float64, pin_memory=True).numpy(),
+                torch.empty(n, dtype=torch.int32, pin_memory=True).numpy())
+        for _ in range(2):
+            r = ctx.evolve(mphi, g, mntot, out=outs)
+            assert r[0] is outs[0] and r[2] is outs[2] and np.array_equal(r[0], ref[0], equal_nan=True) and np.array_equal(r[1], ref[1], equal_nan=True) and np.array_equal(r[2], ref[2])
+        with pytest.raises(ValueError):
+            ctx.evolve(mphi, g, mntot, out=(np.zeros((n, 3, N), dtype=np.float32), None, None))
         # one output only
         ff = torch.empty((n, 3, N), dtype=torch.float64, pin_memory=True).numpy()
         assert ctx._lib.nusi_evolve_batch(ctx._h, n, _dp(mphi), _dp(g), _dp(mntot), None, _dp(ff), None) == 0
