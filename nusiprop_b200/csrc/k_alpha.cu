@@ -57,6 +57,69 @@ edges_kernel(DeviceGrid G, int nE, const PointParams *__restrict__ params, const
   }
 }
 
+// Edge data for the scan builder: alpha_group_kernel reads the FULL edge block only of the first point of a group (the
+// g-independent fields are the group's) and, of every other point, just the seven fields that contain g -- row edge lam2,
+// lnD, phi; column edge lam, args, lnN; the s-channel column factor.  One CTA = (128 edge tasks, an eighth of a group): the first point
+// gets everything, the others those seven (same expressions as make_row_edge / make_col_edge: same bits), which saves
+// two thirds of the logarithms and of the 117 KB per point that edges_kernel writes.
+__global__ void __launch_bounds__(128)
+edges_group_kernel(DeviceGrid G, int nE, const PointParams *__restrict__ params, const double *__restrict__ edgeE,
+                   const int2 *__restrict__ groups, double *__restrict__ edges) {
+  const int2 grp = __ldg(groups + blockIdx.y);
+  const int p0 = grp.x, glen = grp.y;
+  if (params[p0].mphi <= 0) return;
+  const int N = G.N, NT = G.NT;
+  const int per_k = 2 * nE + NT;
+  const int task = blockIdx.x * blockDim.x + threadIdx.x;
+  if (task >= 3 * per_k) return;
+  const int k = task / per_k, q = task - k * per_k;
+  const size_t eblock = edge_block_doubles(nE, NT);
+  for (int j = blockIdx.z; j < glen; j += gridDim.z) {  // gridDim.z CTAs share a group
+    const PointParams P = params[p0 + j];
+    const double mn = P.mn[k], gr = P.Ga / P.mphi;
+    double *base = edges + (size_t)(p0 + j) * eblock;
+    double *gR = base + (size_t)k * NUSI_RF * nE;
+    double *gC = base + (size_t)3 * NUSI_RF * nE + (size_t)k * NUSI_CF * nE;
+    double *gF = base + (size_t)3 * (NUSI_RF + NUSI_CF) * nE + (size_t)k * NUSI_FF * NT;
+    if (q < nE) {
+      const double t = t_of(mn, edgeE[q], P.mphi);
+      if (j == 0) {
+        RowEdge Re;
+        make_row_edge(t, gr, true, Re);
+        gR[0 * nE + q] = Re.t; gR[1 * nE + q] = Re.l1m; gR[2 * nE + q] = Re.labs; gR[3 * nE + q] = Re.lfabs; gR[4 * nE + q] = Re.lam2;
+        gR[5 * nE + q] = Re.argn; gR[6 * nE + q] = Re.lnD; gR[7 * nE + q] = Re.phi; gR[8 * nE + q] = Re.i1p; gR[9 * nE + q] = Re.i1m;
+      } else {
+        const double lam2 = nlog1p(sqr(2 + t) / sqr(gr));
+        gR[4 * nE + q] = lam2;
+        gR[6 * nE + q] = lam2 + 2 * nlog(gr);
+        gR[7 * nE + q] = natan2(gr, 2 + t);
+      }
+    } else if (q < 2 * nE) {
+      const int e = q - nE;
+      const double sv = s_of(mn, edgeE[e], P.mphi);
+      if (j == 0) {
+        ColEdge Ce;
+        make_col_edge(sv, gr, true, Ce);
+        gC[0 * nE + e] = Ce.s; gC[1 * nE + e] = Ce.ls; gC[2 * nE + e] = Ce.lam; gC[3 * nE + e] = Ce.args; gC[4 * nE + e] = Ce.l2s;
+        gC[5 * nE + e] = Ce.ls2; gC[6 * nE + e] = Ce.l2; gC[7 * nE + e] = Ce.lnN; gC[8 * nE + e] = Ce.is;
+      } else {
+        const double lam = nlog1p(sqr(-1 + sv) / sqr(gr));
+        gC[2 * nE + e] = lam;
+        gC[3 * nE + e] = natan2(gr, -1 + sv);
+        gC[7 * nE + e] = lam + 2 * nlog(gr);
+      }
+    } else {
+      const int b = q - 2 * nE;
+      const double sm = s_of(mn, edgeE[edge_lo_id(b, N)], P.mphi), sp = s_of(mn, edgeE[edge_hi_id(b, N)], P.mphi);
+      gF[0 * NT + b] = alpha_s_colfactor(P, sm, sp);
+      if (j == 0) {
+        gF[1 * NT + b] = nlog(sm / sp);
+        gF[2 * NT + b] = nlog(sp / sm);
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // cross-section builder, compact tiled form (MODE 2, default for Majorana + non-resonant).
 //
@@ -452,6 +515,12 @@ cudaError_t launch_edges(const BuildArgs &A, cudaStream_t s) {
   const int ntask = 3 * (2 * A.nE + A.G.NT);
   dim3 ge((ntask + 127) / 128, A.cnt);
   edges_kernel<<<ge, 128, 0, s>>>(A.G, A.nE, A.params, A.edgeE, A.edges);
+  return cudaGetLastError();
+}
+cudaError_t launch_edges_group(const BuildArgs &A, cudaStream_t s) {  // only for a launch that alpha_group_kernel consumes
+  const int ntask = 3 * (2 * A.nE + A.G.NT);
+  dim3 ge((ntask + 127) / 128, A.ngroups, 8);
+  edges_group_kernel<<<ge, 128, 0, s>>>(A.G, A.nE, A.params, A.edgeE, A.groups, A.edges);
   return cudaGetLastError();
 }
 cudaError_t launch_alpha_group(const BuildArgs &A, cudaStream_t s) {

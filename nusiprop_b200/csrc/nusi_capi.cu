@@ -588,15 +588,19 @@ static int launch_alpha_stage(nusi_ctx *c, const BuildArgs &A, cudaStream_t s) {
   const DeviceGrid &G = c->G;
   const int mode = c->opt.elementary_mode;
   if (c->use_tiles) {
-    CU(launch_edges(A, s));
     // the scan builder pays off from ~1.3 points per group on (measured on B200, 8192 points: groups of 1: 45.3 ms,
     // of 2: 31.7, of 8: 18.3, of 32: 14.5; compact builder 42.0 ms)
-    if (mode >= 3 && A.groups && A.ngroups > 0 && !G.phiphi && (4 * (long long)A.ngroups <= 3 * (long long)A.cnt || c->opt.group_always))
+    const bool scan = mode >= 3 && A.groups && A.ngroups > 0 && !G.phiphi && (4 * (long long)A.ngroups <= 3 * (long long)A.cnt || c->opt.group_always);
+    if (scan) {
+      CU(launch_edges_group(A, s));  // full edge data for the first point of a group, the g-dependent fields for the others
       CU(launch_alpha_group(A, s));  // one CTA per (tile, group of points with the same mphi and neutrino masses)
-    else if (mode >= 2)
-      CU(launch_alpha_compact(A, s));
-    else
-      CU(launch_alpha_tile(A, mode, s));
+    } else {
+      CU(launch_edges(A, s));
+      if (mode >= 2)
+        CU(launch_alpha_compact(A, s));
+      else
+        CU(launch_alpha_tile(A, mode, s));
+    }
     c->n_launches += 2;
   } else {
     CU(launch_alpha_entry(A, mode >= 2 ? 1 : 0, s));

@@ -34,6 +34,7 @@ cudaError_t launch_rows(const BuildArgs &A, bool grouped, int split, cudaStream_
 // k_alpha.cu -- alpha table, product builders (nuSIprop.hpp:1237-1520)
 cudaError_t alpha_setup_attributes();
 cudaError_t launch_edges(const BuildArgs &A, cudaStream_t s);
+cudaError_t launch_edges_group(const BuildArgs &A, cudaStream_t s);
 cudaError_t launch_alpha_group(const BuildArgs &A, cudaStream_t s);
 cudaError_t launch_alpha_compact(const BuildArgs &A, cudaStream_t s);
 size_t alpha_group_smem_bytes();
