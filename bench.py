@@ -236,7 +236,8 @@ def roofline(peak, points, steps, ms_kernel, pipeline_slice=2048):
         return out, 0.0, 0.0, 0.0
     # the default integrator at N_E <= 224 is integrate_split_kernel (integrate_diag_kernel before r02_v3 and for opts.integrator = 3)
     integ = "integrate_split_kernel" if "integrate_split_kernel" in prof else "integrate_diag_kernel"
-    fam = {"alpha_kernel": ["alpha_group_kernel", "edges_kernel"], "integrate_kernel": [integ],
+    edges = "edges_group_kernel" if "edges_group_kernel" in prof else "edges_kernel"  # the scan builder's edge kernel since r02_v11
+    fam = {"alpha_kernel": ["alpha_group_kernel", edges], "integrate_kernel": [integ],
            "rows_kernel": ["rows_group_kernel<0>", "rows_group_kernel<1>"]}
     kernels, tot_flop, tot_busy, tot_ms = {}, 0.0, 0.0, 0.0
     for key, names in fam.items():
