@@ -72,7 +72,8 @@ struct nusi_ctx {
   // per-launch work space (grown on demand): slot i of rows / tri / edges / work / stat belongs to point i of a chunk
   int cap_points = 0;
   size_t tstride = 0;
-  double *d_rows = nullptr, *d_tri = nullptr, *d_work = nullptr, *d_edges = nullptr;
+  double *d_rows = nullptr, *d_tri = nullptr, *d_work = nullptr, *d_edges = nullptr, *d_rowsh = nullptr;
+  int rowsh_groups = 0;  // groups of one launch that d_rowsh holds (a quarter of the slots: launches with more, shorter groups use the one-kernel rows)
   int max_chunk = 0;
   // host-buffer path (nusi_evolve_batch): device staging of the outputs, page-locked host staging, streams
   double *d_out_fm = nullptr, *d_out_ff = nullptr, *d_eint = nullptr;
@@ -154,11 +155,12 @@ int nusi_masses(double mntot, int normal_ordering, double mn[3]) {
 }
 
 static void free_workspace(nusi_ctx *c) {
-  for (double **p : {&c->d_rows, &c->d_tri, &c->d_work, &c->d_edges}) {
+  for (double **p : {&c->d_rows, &c->d_tri, &c->d_work, &c->d_edges, &c->d_rowsh}) {
     if (*p) cudaFree(*p);
     *p = nullptr;
   }
   c->cap_points = 0;
+  c->rowsh_groups = 0;
 }
 
 void nusi_ctx_destroy(nusi_ctx *c) {
@@ -504,15 +506,18 @@ static void prepare_points(nusi_ctx *c, int n, const double *mphi, const double 
 static int ensure_workspace(nusi_ctx *c, int npts) {
   if (npts <= c->cap_points) return NUSI_OK;
   CU(cudaDeviceSynchronize());  // nothing in flight uses the old buffers
-  double *rows = nullptr, *tri = nullptr, *work = nullptr, *edges = nullptr;
+  double *rows = nullptr, *tri = nullptr, *work = nullptr, *edges = nullptr, *rowsh = nullptr;
+  const int rowsh_groups = npts / 4 + 64;
   cudaError_t e = cudaMalloc((void **)&rows, (size_t)npts * 2 * c->H.NT * sizeof(double));
   // + 16 bytes: the integrator's 16-byte-granular bulk copies may read one double past the last column
   if (e == cudaSuccess) e = cudaMalloc((void **)&tri, (size_t)npts * c->tstride * sizeof(double) + 16);
   if (e == cudaSuccess && !c->G.non_resonant) e = cudaMalloc((void **)&work, (size_t)npts * 3 * c->H.N * sizeof(double));
   if (e == cudaSuccess && c->use_tiles)
     e = cudaMalloc((void **)&edges, (size_t)npts * edge_block_doubles(c->n_edges, c->H.NT) * sizeof(double));
+  if (e == cudaSuccess && c->G.majorana && c->G.non_resonant && !c->G.phiphi)
+    e = cudaMalloc((void **)&rowsh, (size_t)rowsh_groups * c->H.NT * 3 * NUSI_ROWSH * sizeof(double));
   if (e != cudaSuccess) {
-    for (double *p : {rows, tri, work, edges})
+    for (double *p : {rows, tri, work, edges, rowsh})
       if (p) cudaFree(p);
     cudaGetLastError();
     return fail(NUSI_E_NOMEM, std::string("work space for ") + std::to_string(npts) + " points: " + cudaGetErrorString(e));
@@ -522,6 +527,8 @@ static int ensure_workspace(nusi_ctx *c, int npts) {
   c->d_tri = tri;
   c->d_work = work;
   c->d_edges = edges;
+  c->d_rowsh = rowsh;
+  c->rowsh_groups = rowsh ? rowsh_groups : 0;
   c->cap_points = npts;
   return NUSI_OK;
 }
@@ -559,6 +566,8 @@ static BuildArgs build_args(const nusi_ctx *c, int wo, const PointParams *d_para
   A.n_ctiles = c->n_ctiles;
   A.groups = d_groups;
   A.ngroups = ngroups;
+  A.rowsh = c->d_rowsh;  // one launch at a time per stream uses it (the row kernels of consecutive slices are stream-ordered)
+  A.rowsh_groups = c->rowsh_groups;
   return A;
 }
 
@@ -576,10 +585,13 @@ static int launch_rows_stage(nusi_ctx *c, const BuildArgs &A, cudaStream_t s) {
     const long long nblk = (G.NT + NUSI_ROWS_PER_CTA - 1) / NUSI_ROWS_PER_CTA;
     const long long want = 1184, have = nblk * A.ngroups * split;
     if (have < want) split = (int)std::min<long long>(32, (want + nblk * A.ngroups - 1) / (nblk * A.ngroups));
+    // two-kernel rows (shared part once per group in its own kernel): nothing is repeated, so the per-point kernel takes two
+    // points of a 32-point group per CTA (B200, 8192 points: 4 / 8 / 16 / 32 CTAs per group 2.97 / 2.70 / 2.61 / 2.63 ms)
+    if (A.rowsh && A.ngroups <= A.rowsh_groups) split = std::max(split, 16);
     if (c->opt.rows_split > 0) split = c->opt.rows_split;
   }
   CU(launch_rows(A, grouped, split, s));
-  c->n_launches += 2;
+  c->n_launches += (grouped && A.rowsh && A.ngroups <= A.rowsh_groups) ? 4 : 2;  // shared part + per-point part per function
   return NUSI_OK;
 }
 

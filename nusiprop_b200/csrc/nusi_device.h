@@ -49,6 +49,7 @@ NUSI_HD size_t edge_block_doubles(int nE, int NT) {
 }
 #define NUSI_CE 16  // edges per tile side of the compact / scan builders
 #define NUSI_ROWS_PER_CTA 64
+#define NUSI_ROWSH 17  // doubles per (group, row, target mass) of the row kernels' g-independent part (>= sizeof(GammaShared), sizeof(ATildeShared))
 
 }  // namespace nusi
 #endif

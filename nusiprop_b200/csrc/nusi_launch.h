@@ -26,6 +26,8 @@ struct BuildArgs {
   int n_ctiles;
   const int2 *groups;         // scan builders: (first point, length) of runs with identical (mphi, m_nu)
   int ngroups;
+  double *rowsh;              // scan rows: [rowsh_groups][NT][3][NUSI_ROWSH] g-independent part per (group, row, mass), or NULL
+  int rowsh_groups;
 };
 
 // k_rows.cu -- Gamma / alphaTilde rows (nuSIprop.hpp:759-1235)

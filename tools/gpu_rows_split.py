@@ -8,7 +8,7 @@ import nusiprop_b200 as nb, bench
 m, g = bench.shard(0)
 cfg = dict(N_bins_E=200, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2)
 ref = None
-for sp in (0, 1, 2, 3, 4, 6, 8, 16):
+for sp in (0, 8, 12, 16, 24, 32):
     ctx = nb.Context(rows_split=sp, **cfg)
     for _ in range(3):
         out = ctx.evolve(m, g, 0.1)
