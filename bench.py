@@ -238,7 +238,8 @@ def roofline(peak, points, steps, ms_kernel, pipeline_slice=2048):
     integ = "integrate_split_kernel" if "integrate_split_kernel" in prof else "integrate_diag_kernel"
     edges = "edges_group_kernel" if "edges_group_kernel" in prof else "edges_kernel"  # the scan builder's edge kernel since r02_v11
     fam = {"alpha_kernel": ["alpha_group_kernel", edges], "integrate_kernel": [integ],
-           "rows_kernel": ["rows_group_kernel<0>", "rows_group_kernel<1>"]}
+           "rows_kernel": ([n for n in ("rows_shared_kernel<0>", "rows_point_kernel<0>", "rows_shared_kernel<1>", "rows_point_kernel<1>") if n in prof]
+                           or ["rows_group_kernel<0>", "rows_group_kernel<1>"])}  # two kernels per function since r02_v12
     kernels, tot_flop, tot_busy, tot_ms = {}, 0.0, 0.0, 0.0
     for key, names in fam.items():
         ms = ms_kernel.get(key, 0.0)

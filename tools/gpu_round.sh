@@ -22,8 +22,8 @@ ncu)
   python bench.py $ARGS > ${O}_plain.log 2>&1 || { echo "plain run failed"; tail -5 ${O}_plain.log; continue; }
   ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file ${O}_launches.csv python bench.py $ARGS > ${O}_ncu_launch.log 2>&1
   echo "ncu launches exit=$?"
-  # per slice: rows_group<0>, rows_group<1>, edges_group, alpha_group, integrate_split; skip the warm-up step's five
-  ncu --set full --clock-control none --import-source on -k regex:"rows_group|edges_|alpha_group|integrate_split|integrate_diag" -s 5 -c 5 -f \
+  # per slice: rows_shared<0>, rows_point<0>, rows_shared<1>, rows_point<1>, edges_group, alpha_group, integrate_split; skip the warm-up step's seven
+  ncu --set full --clock-control none --import-source on -k regex:"rows_|edges_|alpha_group|integrate_split|integrate_diag" -s 7 -c 7 -f \
       -o ${O}_prof python bench.py $ARGS > ${O}_ncu_full.log 2>&1
   echo "ncu full exit=$?"
   ;;
