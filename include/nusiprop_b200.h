@@ -96,8 +96,9 @@ typedef struct nusi_opts {
                                 groups are cut, so the scan builder's gain does not depend on the caller's order;
                                 results always come back in the caller's order */
   int two_stream;        /* 1 = builder and rows + integrator on two streams: the integrator of a slice runs beside the builder
-                                of the next one (r02: 20.63 instead of 21.01 ms per 8192 points, same bits; not the default
-                                because per-kernel event times then overlap and no longer add up to the step) */
+                                of the next one (r02: 20.31 instead of 20.54 ms per 8192 points, same bits; not the default:
+                                the per-kernel event times then include each other -- the builder reads 16.7 instead of 14.4 ms --
+                                and no longer add up to the step, which is what the bench's per-kernel roofline is built on) */
   int source_device;     /* source_model 0: 0 = Lum(z_i, bin j) computed on the host (same glibc calls as the reference,
                                 bit-identical to it) and uploaded; 1 = computed by the CUDA source kernel (device exp / log
                                 + Li2 / Li3; differs from the host array by up to 1e-6 in the four lowest bins, where the

@@ -586,3 +586,38 @@ def test_cluster_integrator_with_rejected_points_and_reordering(nusi):
     assert np.array_equal(a[2], b[2]) and np.isfinite(a[0][ok]).all()
     assert np.array_equal(a[0][ok], clean[0][ok]) and np.array_equal(a[1][ok], clean[1][ok])  # neighbours untouched, bit for bit
     assert np.all(np.abs(a[0][ok] - b[0][ok]) <= 1e-14 * np.abs(b[0][ok]) + 1e-300)
+
+
+def test_two_streams_and_one_stream_give_the_same_bits(nusi):
+    """opts.two_stream: the builder on one stream, rows + integrator on another (the integrator of a slice beside the builder of
+    the next) against everything on the caller's stream: same bits through both entry points, for several slices, a ragged
+    last slice, a reordered batch, a small max_points_per_launch (the work space is reused between chunks) and N_E = 700."""
+    import torch
+    for cfg, n, extra in ((CFG200, 2048 * 2 + 300, {}), (CFG200, 1500, dict(max_points_per_launch=512)),
+                          (dict(N_bins_E=700, lEmin=4.0, lEmax=9.0, zmax=5.0, flav=2), 70, {})):
+        m = np.repeat(10 ** np.linspace(1.2, 3.8, (n + 31) // 32), 32)[:n]
+        g = np.tile(10 ** np.linspace(-4.5, -0.5, 32), (n + 31) // 32)[:n]
+        perm = np.random.default_rng(9).permutation(n)
+        res = {}
+        for ts in (0, 1):
+            ctx = nusi.Context(two_stream=ts, **cfg, **extra)
+            a = ctx.evolve(m, g, 0.1)                 # host buffers, scan order
+            b = ctx.evolve(m[perm], g[perm], 0.1)     # reordered by the library, scattered back
+            pts = ctx.upload_points(m, g, np.full(n, 0.1))
+            N = ctx.N_bins_E
+            fm = torch.empty((n, 3, N), dtype=torch.float64, device="cuda")
+            ff, st = torch.empty_like(fm), torch.zeros(n, dtype=torch.int32, device="cuda")
+            for _ in range(2):
+                ctx.evolve_points(pts, fm.data_ptr(), ff.data_ptr(), st.data_ptr(), torch.cuda.current_stream().cuda_stream)
+            torch.cuda.synchronize()
+            res[ts] = (a, b, fm.cpu().numpy(), ff.cpu().numpy(), st.cpu().numpy())
+            pts.close()
+            ctx.close()
+        a0, b0, fm0, ff0, st0 = res[0]
+        a1, b1, fm1, ff1, st1 = res[1]
+        for x, y in zip(a0, a1):
+            assert np.array_equal(x, y, equal_nan=True)
+        for x, y in zip(b0, b1):
+            assert np.array_equal(x, y, equal_nan=True)
+        assert np.array_equal(b0[0][np.argsort(perm)], a0[0], equal_nan=True)
+        assert np.array_equal(fm0, fm1) and np.array_equal(ff0, ff1) and np.array_equal(st0, st1) and np.array_equal(fm0, a0[0])
